@@ -1,0 +1,424 @@
+// hetseq_b200 -- persistent, warp-specialised tcgen05 GEMM for sm_100a.
+//
+//   C[M,N] = epilogue( alpha * sum_k A(m,k) * B(n,k) )        fp16/bf16 in, fp32 accumulate in TMEM
+//
+// One CTA per SM loops over 128 x BN output tiles. Warp roles:
+//   warp 0   TMA producer: cp.async.bulk.tensor tiles of A and B into a STAGES-deep smem ring
+//   warp 1   MMA issuer:   one elected thread issues tcgen05.mma (128 x BN x 16) per k-step, commits
+//                          ring slots back to the producer and finished accumulators to the epilogue
+//   warps 2-9 epilogue:    tcgen05.ld the accumulator (double-buffered in TMEM, so the next tile's
+//                          MMAs overlap this tile's epilogue), apply bias / GELU / tanh / dGELU /
+//                          accumulate, convert and store
+// Operands may be K-major or MN-major in global memory (both are expressed through the TMA box
+// shape and the UMMA shared-memory descriptor), so forward, dgrad and wgrad all run without any
+// transpose pass:  forward X*W^T = (K,K);  dgrad dY*W = (K,MN);  wgrad dY^T*X = (MN,MN).
+//
+// Replaces the cuBLAS calls behind F.linear / autograd in the reference
+// (bert_modeling.py:352-354,387-391,409-413,423-427,514-515,525-528,547; SURVEY.md K1,K5-K7,K9-K11,K14)
+// and the TorchScript bias_gelu / bias_tanh fusions (bert_modeling.py:104-130,166-172).
+#include "common.cuh"
+#include "host.h"
+#include "../include/hetseq_b200.h"
+
+#include <mutex>
+
+namespace hs {
+
+constexpr int BM = 128;
+constexpr int BK = 64;               // 64 x 16-bit = one 128-byte swizzle row
+constexpr int A_STAGE_BYTES = BM * 128;
+constexpr int EPI_WARPS = 8;             // two warps per TMEM lane quarter, each takes half the columns
+constexpr int GEMM_THREADS = 64 + EPI_WARPS * 32;
+
+struct GemmParams {
+  void* C;
+  const void* bias;
+  void* aux_out;
+  const void* aux_in;
+  int M, N, K, ldc, ldaux;
+  int tiles_m, tiles_n, num_kb;
+  int a_mn, b_mn;
+  uint32_t idesc;
+  uint32_t a_lbo, a_sbo, a_kadv;  // bytes
+  uint32_t b_lbo, b_sbo, b_kadv;
+  int act, accumulate;
+  float alpha;
+  int vec_ok;  // C/aux rows are 16-byte aligned -> vector loads/stores allowed
+};
+
+template <int BN> struct GemmCfg {
+  static constexpr int STAGES = (BN == 256) ? 4 : 6;
+  static constexpr int B_STAGE_BYTES = BN * 128;
+  static constexpr int TMEM_COLS = 2 * BN;
+  static constexpr int SMEM_BYTES = STAGES * (A_STAGE_BYTES + B_STAGE_BYTES) + 2 * BN * 4 /*bias*/ +
+                                    (2 * STAGES + 4) * 8 /*mbarriers*/ + 16 /*tmem slot*/ + 1024 /*align*/;
+};
+
+// ---- epilogue helpers -------------------------------------------------------------------------
+template <typename T>
+__device__ __forceinline__ void load_row32(const T* __restrict__ p, int n0, int N, bool vec, float (&o)[32]) {
+  if (vec && n0 + 32 <= N) {
+    if constexpr (sizeof(T) == 2) {
+      const uint4* q = reinterpret_cast<const uint4*>(p + n0);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        uint4 u = q[i];
+        float2 f0 = Cvt<T>::unpack2(u.x), f1 = Cvt<T>::unpack2(u.y), f2 = Cvt<T>::unpack2(u.z),
+               f3 = Cvt<T>::unpack2(u.w);
+        o[i * 8 + 0] = f0.x; o[i * 8 + 1] = f0.y; o[i * 8 + 2] = f1.x; o[i * 8 + 3] = f1.y;
+        o[i * 8 + 4] = f2.x; o[i * 8 + 5] = f2.y; o[i * 8 + 6] = f3.x; o[i * 8 + 7] = f3.y;
+      }
+    } else {
+      const float4* q = reinterpret_cast<const float4*>(p + n0);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        float4 u = q[i];
+        o[i * 4 + 0] = u.x; o[i * 4 + 1] = u.y; o[i * 4 + 2] = u.z; o[i * 4 + 3] = u.w;
+      }
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) o[i] = (n0 + i < N) ? Cvt<T>::to_f(p[n0 + i]) : 0.0f;
+  }
+}
+
+template <typename T>
+__device__ __forceinline__ void store_row32(T* __restrict__ p, int n0, int N, bool vec, const float (&v)[32]) {
+  if (vec && n0 + 32 <= N) {
+    if constexpr (sizeof(T) == 2) {
+      uint4* q = reinterpret_cast<uint4*>(p + n0);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        uint4 u;
+        u.x = Cvt<T>::pack2(v[i * 8 + 0], v[i * 8 + 1]);
+        u.y = Cvt<T>::pack2(v[i * 8 + 2], v[i * 8 + 3]);
+        u.z = Cvt<T>::pack2(v[i * 8 + 4], v[i * 8 + 5]);
+        u.w = Cvt<T>::pack2(v[i * 8 + 6], v[i * 8 + 7]);
+        q[i] = u;
+      }
+    } else {
+      float4* q = reinterpret_cast<float4*>(p + n0);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) q[i] = make_float4(v[i * 4 + 0], v[i * 4 + 1], v[i * 4 + 2], v[i * 4 + 3]);
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 32; ++i)
+      if (n0 + i < N) p[n0 + i] = Cvt<T>::from_f(v[i]);
+  }
+}
+
+// ---- the kernel -------------------------------------------------------------------------------
+template <int BN, typename InT, typename OutT>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const GemmParams p) {
+  using Cfg = GemmCfg<BN>;
+  constexpr int STAGES = Cfg::STAGES;
+  constexpr int B_STAGE_BYTES = Cfg::B_STAGE_BYTES;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + STAGES * A_STAGE_BYTES;
+  float* sBias = reinterpret_cast<float*>(sB + STAGES * B_STAGE_BYTES);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(sBias + 2 * BN);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tfull_bar = empty_bar + STAGES;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int num_tiles = p.tiles_m * p.tiles_n;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int s = 0; s < STAGES; ++s) {
+        mbar_init(&full_bar[s], 1);
+        mbar_init(&empty_bar[s], 1);
+      }
+      for (int a = 0; a < 2; ++a) {
+        mbar_init(&tfull_bar[a], 1);
+        mbar_init(&tempty_bar[a], EPI_WARPS);  // one arrive per epilogue warp
+      }
+      fence_mbar_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int tm = tile % p.tiles_m, tn = tile / p.tiles_m;
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_expect_tx(&full_bar[stage], A_STAGE_BYTES + B_STAGE_BYTES);
+          uint8_t* a_dst = sA + stage * A_STAGE_BYTES;
+          uint8_t* b_dst = sB + stage * B_STAGE_BYTES;
+          if (!p.a_mn) {
+            tma_load_2d(a_dst, &tmA, &full_bar[stage], kb * BK, tm * BM);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BM / 64; ++j)
+              tma_load_2d(a_dst + j * (BK * 128), &tmA, &full_bar[stage], tm * BM + j * 64, kb * BK);
+          }
+          if (!p.b_mn) {
+            tma_load_2d(b_dst, &tmB, &full_bar[stage], kb * BK, tn * BN);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j)
+              tma_load_2d(b_dst + j * (BK * 128), &tmB, &full_bar[stage], tn * BN + j * 64, kb * BK);
+          }
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    int stage = 0;
+    uint32_t phase = 0;
+    int as = 0;
+    uint32_t aphase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      mbar_wait(&tempty_bar[as], aphase ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + as * BN;
+      for (int kb = 0; kb < p.num_kb; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        if (elect_one_sync()) {
+          const uint32_t a_addr = smem_u32(sA + stage * A_STAGE_BYTES);
+          const uint32_t b_addr = smem_u32(sB + stage * B_STAGE_BYTES);
+          const uint64_t adesc = umma_desc_sw128(a_addr, p.a_lbo, p.a_sbo);
+          const uint64_t bdesc = umma_desc_sw128(b_addr, p.b_lbo, p.b_sbo);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            umma_f16(d_tmem, adesc + ((k * p.a_kadv) >> 4), bdesc + ((k * p.b_kadv) >> 4), p.idesc,
+                     (kb | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);                        // ring slot free once these MMAs retire
+          if (kb == p.num_kb - 1) umma_commit(&tfull_bar[as]);   // accumulator complete
+        }
+        __syncwarp();
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+      if (++as == 2) { as = 0; aphase ^= 1; }
+    }
+  } else {
+    // ===================== epilogue (warps 2..9) =====================
+    const int q = warp & 3;  // TMEM lane quarter this warp may access
+    const int half = (warp - 2) >> 2;  // which half of the tile's columns this warp drains
+    const int et = threadIdx.x - 64;
+    const InT* bias = reinterpret_cast<const InT*>(p.bias);
+    OutT* C = reinterpret_cast<OutT*>(p.C);
+    const bool vec = p.vec_ok != 0;
+    int as = 0;
+    uint32_t aphase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int tm = tile % p.tiles_m, tn = tile / p.tiles_m;
+      const int n_base = tn * BN;
+      float* sb = sBias + as * BN;
+      if (bias != nullptr) {
+        for (int i = et; i < BN; i += EPI_WARPS * 32) sb[i] = (n_base + i < p.N) ? Cvt<InT>::to_f(bias[n_base + i]) : 0.0f;
+      }
+      asm volatile("bar.sync 1, %0;" ::"n"(EPI_WARPS * 32) : "memory");
+      mbar_wait(&tfull_bar[as], aphase);
+      tc_fence_after();
+      const int m = tm * BM + q * 32 + lane;
+      const bool row_ok = m < p.M;
+      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
+#pragma unroll 1
+      for (int cc = 0; cc < BN / 64; ++cc) {
+        const int c = half * (BN / 64) + cc;
+        const int n0 = n_base + c * 32;
+        if (n0 >= p.N) break;  // warp-uniform
+        uint32_t r[32];
+        tmem_ld_32x32(t_row + c * 32, r);
+        tmem_ld_wait();
+        float v[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]) * p.alpha;
+        if (bias != nullptr) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] += sb[c * 32 + i];
+        }
+        if (row_ok) {
+          if (p.act == HS_ACT_GELU) {
+            if (p.aux_out != nullptr) {
+              store_row32<InT>(reinterpret_cast<InT*>(p.aux_out) + static_cast<size_t>(m) * p.ldaux, n0, p.N, vec, v);
+            }
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = gelu_ref(v[i]);
+          } else if (p.act == HS_ACT_TANH) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = tanhf(v[i]);
+          } else if (p.act == HS_ACT_DGELU_MUL) {
+            float x[32];
+            load_row32<InT>(reinterpret_cast<const InT*>(p.aux_in) + static_cast<size_t>(m) * p.ldaux, n0, p.N, vec, x);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] *= gelu_grad_ref(x[i]);
+          }
+          OutT* crow = C + static_cast<size_t>(m) * p.ldc;
+          if (p.accumulate) {
+            float o[32];
+            load_row32<OutT>(crow, n0, p.N, vec, o);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] += o[i];
+          }
+          store_row32<OutT>(crow, n0, p.N, vec, v);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty_bar[as]);
+      if (++as == 2) { as = 0; aphase ^= 1; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+  }
+}
+
+// ---- host side --------------------------------------------------------------------------------
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                    CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                    CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode_fn() {
+  static PFN_encodeTiled fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_encodeTiled>(p);
+  });
+  return fn;
+}
+
+int make_tmap_2d_16b(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t ld,
+                     uint32_t box_inner, uint32_t box_outer) {
+  PFN_encodeTiled enc = get_encode_fn();
+  if (enc == nullptr) {
+    set_last_error("cuTensorMapEncodeTiled is not available from the CUDA driver");
+    return 1;
+  }
+  cuuint64_t dims[2] = {inner, outer};
+  cuuint64_t strides[1] = {ld * 2};
+  cuuint32_t box[2] = {box_inner, box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_last_error("cuTensorMapEncodeTiled failed (%d): base=%p inner=%llu outer=%llu ld=%llu box=%ux%u", (int)r,
+                   base, (unsigned long long)inner, (unsigned long long)outer, (unsigned long long)ld, box_inner,
+                   box_outer);
+    return 1;
+  }
+  return 0;
+}
+
+template <int BN, typename InT, typename OutT>
+static int launch_gemm(const hs_gemm_args& a, cudaStream_t stream) {
+  using Cfg = GemmCfg<BN>;
+  auto kern = gemm_tcgen05_kernel<BN, InT, OutT>;
+  static bool attr_done[64] = {false};
+  int dev = 0;
+  HS_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 64 && !attr_done[dev]) {
+    HS_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    attr_done[dev] = true;
+  }
+  CUtensorMap tmA, tmB;
+  int rc;
+  if (!a.a_mn_major) rc = make_tmap_2d_16b(&tmA, a.A, a.K, a.M, a.lda, BK, BM);
+  else               rc = make_tmap_2d_16b(&tmA, a.A, a.M, a.K, a.lda, 64, BK);
+  if (rc) return rc;
+  if (!a.b_mn_major) rc = make_tmap_2d_16b(&tmB, a.B, a.K, a.N, a.ldb, BK, BN);
+  else               rc = make_tmap_2d_16b(&tmB, a.B, a.N, a.K, a.ldb, 64, BK);
+  if (rc) return rc;
+
+  GemmParams p;
+  p.C = a.C; p.bias = a.bias; p.aux_out = a.aux_out; p.aux_in = a.aux_in;
+  p.M = a.M; p.N = a.N; p.K = a.K; p.ldc = a.ldc; p.ldaux = a.ldaux;
+  p.tiles_m = (a.M + BM - 1) / BM;
+  p.tiles_n = (a.N + BN - 1) / BN;
+  p.num_kb = (a.K + BK - 1) / BK;
+  p.a_mn = a.a_mn_major; p.b_mn = a.b_mn_major;
+  p.idesc = umma_idesc_f16(a.in_dtype == HS_BF16 ? 1 : 0, a.a_mn_major, a.b_mn_major, BM, BN);
+  // K-major, 128B swizzle: 8-row groups 1024 B apart; a k-step of 16 elements is 32 B inside the row.
+  // MN-major, 128B swizzle: 64-element MN groups are separate TMA boxes (BK*128 B apart), 8-k groups
+  // 1024 B apart; a k-step of 16 rows is 2048 B.
+  p.a_lbo = a.a_mn_major ? BK * 128 : 16; p.a_sbo = 1024; p.a_kadv = a.a_mn_major ? 2048 : 32;
+  p.b_lbo = a.b_mn_major ? BK * 128 : 16; p.b_sbo = 1024; p.b_kadv = a.b_mn_major ? 2048 : 32;
+  p.act = a.act; p.accumulate = a.accumulate; p.alpha = a.alpha;
+  const size_t osz = sizeof(OutT);
+  bool vec = (reinterpret_cast<uintptr_t>(a.C) % 16 == 0) && ((a.ldc * osz) % 16 == 0);
+  if (a.aux_out) vec = vec && (reinterpret_cast<uintptr_t>(a.aux_out) % 16 == 0) && ((a.ldaux * 2) % 16 == 0);
+  if (a.aux_in) vec = vec && (reinterpret_cast<uintptr_t>(a.aux_in) % 16 == 0) && ((a.ldaux * 2) % 16 == 0);
+  p.vec_ok = vec ? 1 : 0;
+
+  const int tiles = p.tiles_m * p.tiles_n;
+  const int grid = tiles < num_sms() ? tiles : num_sms();
+  kern<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, p);
+  return post_launch("gemm_tcgen05_kernel");
+}
+
+template <int BN>
+static int dispatch_types(const hs_gemm_args& a, cudaStream_t s) {
+  if (a.in_dtype == HS_F16) {
+    if (a.out_dtype == HS_F16) return launch_gemm<BN, __half, __half>(a, s);
+    if (a.out_dtype == HS_F32) return launch_gemm<BN, __half, float>(a, s);
+  } else if (a.in_dtype == HS_BF16) {
+    if (a.out_dtype == HS_BF16) return launch_gemm<BN, __nv_bfloat16, __nv_bfloat16>(a, s);
+    if (a.out_dtype == HS_F32) return launch_gemm<BN, __nv_bfloat16, float>(a, s);
+  }
+  set_last_error("hs_gemm: unsupported dtype combination in=%d out=%d", a.in_dtype, a.out_dtype);
+  return 1;
+}
+
+}  // namespace hs
+
+extern "C" int hs_gemm(const hs_gemm_args* args, hs_stream_t stream) {
+  using namespace hs;
+  if (args == nullptr) { set_last_error("hs_gemm: null args"); return 1; }
+  const hs_gemm_args& a = *args;
+  if (a.M <= 0 || a.N <= 0 || a.K <= 0) { set_last_error("hs_gemm: empty problem %dx%dx%d", a.M, a.N, a.K); return 1; }
+  if (a.lda % 8 || a.ldb % 8) { set_last_error("hs_gemm: lda/ldb must be multiples of 8 (got %d, %d)", a.lda, a.ldb); return 1; }
+  if ((reinterpret_cast<uintptr_t>(a.A) | reinterpret_cast<uintptr_t>(a.B)) % 16) {
+    set_last_error("hs_gemm: A and B must be 16-byte aligned");
+    return 1;
+  }
+  if (a.act == HS_ACT_DGELU_MUL && a.aux_in == nullptr) { set_last_error("hs_gemm: DGELU_MUL needs aux_in"); return 1; }
+  // Tile-width heuristic: prefer 128x256 tiles (fewer B re-reads) unless 128x128 fills the SMs better.
+  const int sms = num_sms();
+  const long tm = (a.M + BM - 1) / BM;
+  const long t256 = tm * ((a.N + 255) / 256), t128 = tm * ((a.N + 127) / 128);
+  auto waves_cost = [&](long tiles, int bn) {  // time ~ waves * tile cost
+    const long waves = (tiles + sms - 1) / sms;
+    return static_cast<double>(waves) * bn;
+  };
+  const bool use256 = a.N > 128 && waves_cost(t256, 256) <= waves_cost(t128, 128);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  return use256 ? dispatch_types<256>(a, s) : dispatch_types<128>(a, s);
+}

@@ -1,0 +1,222 @@
+// Standalone numerics + throughput harness for hs_gemm (no torch needed):
+//   nvcc ... csrc/tests/gemm_test.cu csrc/gemm_sm100.cu csrc/lib.cu -o build/gemm_test && ./build/gemm_test
+// Every case is checked against a double-precision CPU restatement of the same math.
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+#include <cuda_bf16.h>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+#include "../../include/hetseq_b200.h"
+
+#define CK(x)                                                                              \
+  do {                                                                                     \
+    cudaError_t e_ = (x);                                                                  \
+    if (e_ != cudaSuccess) {                                                               \
+      printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e_), __FILE__, __LINE__);      \
+      exit(2);                                                                             \
+    }                                                                                      \
+  } while (0)
+
+static uint32_t rng_state = 12345u;
+static float frand() {
+  rng_state = rng_state * 1664525u + 1013904223u;
+  return ((rng_state >> 8) & 0xFFFF) / 65536.0f - 0.5f;
+}
+
+static uint16_t f2h(float f, int bf) {
+  if (bf) { __nv_bfloat16 b = __float2bfloat16(f); uint16_t u; memcpy(&u, &b, 2); return u; }
+  __half h = __float2half(f); uint16_t u; memcpy(&u, &h, 2); return u;
+}
+static float h2f(uint16_t u, int bf) {
+  if (bf) { __nv_bfloat16 b; memcpy(&b, &u, 2); return __bfloat162float(b); }
+  __half h; memcpy(&h, &u, 2); return __half2float(h);
+}
+static double gelu_d(double x) { return x * 0.5 * (1.0 + erf(x / 1.41421)); }
+static double dgelu_d(double x) {
+  double u = x / 1.41421;
+  return 0.5 * (1.0 + erf(u)) + x * exp(-u * u) / (1.41421 * sqrt(M_PI));
+}
+
+struct Case {
+  int M, N, K, a_mn, b_mn, bf, out_f32, bias, act, accumulate;
+  const char* name;
+};
+
+static int run_case(const Case& c) {
+  const int M = c.M, N = c.N, K = c.K;
+  auto r8 = [](int x) { return (x + 7) / 8 * 8; };
+  const int lda = c.a_mn ? r8(M) : r8(K), ldb = c.b_mn ? r8(N) : r8(K), ldc = r8(N) + 8, ldaux = r8(N);
+  const size_t a_rows = c.a_mn ? K : M, b_rows = c.b_mn ? K : N;
+  std::vector<uint16_t> hA(a_rows * lda, 0), hB(b_rows * ldb, 0), hbias(N), haux((size_t)M * ldaux, 0);
+  std::vector<float> fA((size_t)M * K), fB((size_t)N * K);
+  for (int m = 0; m < M; ++m)
+    for (int k = 0; k < K; ++k) {
+      uint16_t u = f2h(frand(), c.bf);
+      fA[(size_t)m * K + k] = h2f(u, c.bf);
+      if (c.a_mn) hA[(size_t)k * lda + m] = u; else hA[(size_t)m * lda + k] = u;
+    }
+  for (int n = 0; n < N; ++n)
+    for (int k = 0; k < K; ++k) {
+      uint16_t u = f2h(frand(), c.bf);
+      fB[(size_t)n * K + k] = h2f(u, c.bf);
+      if (c.b_mn) hB[(size_t)k * ldb + n] = u; else hB[(size_t)n * ldb + k] = u;
+    }
+  for (int n = 0; n < N; ++n) hbias[n] = f2h(frand(), c.bf);
+  for (size_t i = 0; i < haux.size(); ++i) haux[i] = f2h(frand() * 4.0f, c.bf);
+  const size_t csz = c.out_f32 ? 4 : 2;
+  std::vector<uint8_t> hC((size_t)M * ldc * csz);
+  std::vector<float> c_init((size_t)M * ldc, 0.f);
+  for (size_t i = 0; i < c_init.size(); ++i) {
+    float v = c.accumulate ? frand() : 777.0f;
+    if (c.out_f32) memcpy(&hC[i * 4], &v, 4);
+    else { uint16_t u = f2h(v, c.bf); memcpy(&hC[i * 2], &u, 2); v = h2f(u, c.bf); }
+    c_init[i] = v;
+  }
+  void *dA, *dB, *dC, *dbias, *daux_in, *daux_out;
+  CK(cudaMalloc(&dA, hA.size() * 2)); CK(cudaMalloc(&dB, hB.size() * 2)); CK(cudaMalloc(&dC, hC.size()));
+  CK(cudaMalloc(&dbias, N * 2)); CK(cudaMalloc(&daux_in, haux.size() * 2)); CK(cudaMalloc(&daux_out, haux.size() * 2));
+  CK(cudaMemcpy(dA, hA.data(), hA.size() * 2, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dB, hB.data(), hB.size() * 2, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dC, hC.data(), hC.size(), cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dbias, hbias.data(), N * 2, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(daux_in, haux.data(), haux.size() * 2, cudaMemcpyHostToDevice));
+  CK(cudaMemset(daux_out, 0, haux.size() * 2));
+
+  hs_gemm_args g; memset(&g, 0, sizeof(g));
+  g.A = dA; g.B = dB; g.C = dC; g.M = M; g.N = N; g.K = K; g.lda = lda; g.ldb = ldb; g.ldc = ldc;
+  g.a_mn_major = c.a_mn; g.b_mn_major = c.b_mn; g.in_dtype = c.bf ? HS_BF16 : HS_F16;
+  g.out_dtype = c.out_f32 ? HS_F32 : g.in_dtype; g.bias = c.bias ? dbias : nullptr; g.act = c.act;
+  g.aux_out = (c.act == HS_ACT_GELU) ? daux_out : nullptr; g.aux_in = (c.act == HS_ACT_DGELU_MUL) ? daux_in : nullptr;
+  g.ldaux = ldaux; g.accumulate = c.accumulate; g.alpha = 1.0f;
+  int rc = hs_gemm(&g, nullptr);
+  if (rc) { printf("FAIL %-28s launch error: %s\n", c.name, hs_last_error()); return 1; }
+  cudaError_t e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) { printf("FAIL %-28s runtime error: %s\n", c.name, cudaGetErrorString(e)); exit(3); }
+  CK(cudaMemcpy(hC.data(), dC, hC.size(), cudaMemcpyDeviceToHost));
+  std::vector<uint16_t> haux_out(haux.size());
+  CK(cudaMemcpy(haux_out.data(), daux_out, haux.size() * 2, cudaMemcpyDeviceToHost));
+
+  double max_err = 0, max_aux_err = 0; long bad = 0; int shown = 0;
+  for (int m = 0; m < M; ++m)
+    for (int n = 0; n < N; ++n) {
+      double acc = 0;
+      const float* a = &fA[(size_t)m * K]; const float* b = &fB[(size_t)n * K];
+      for (int k = 0; k < K; ++k) acc += (double)a[k] * b[k];
+      if (c.bias) acc += h2f(hbias[n], c.bf);
+      double pre = acc;
+      if (c.act == HS_ACT_GELU) acc = gelu_d(acc);
+      else if (c.act == HS_ACT_TANH) acc = tanh(acc);
+      else if (c.act == HS_ACT_DGELU_MUL) acc *= dgelu_d(h2f(haux[(size_t)m * ldaux + n], c.bf));
+      if (c.accumulate) acc += c_init[(size_t)m * ldc + n];
+      float got;
+      if (c.out_f32) memcpy(&got, &hC[((size_t)m * ldc + n) * 4], 4);
+      else { uint16_t u; memcpy(&u, &hC[((size_t)m * ldc + n) * 2], 2); got = h2f(u, c.bf); }
+      double tol = (c.out_f32 ? 2e-3 : (c.bf ? 2e-2 : 4e-3)) * (1.0 + fabs(acc));
+      double err = fabs(got - acc);
+      if (err > max_err) max_err = err;
+      if (!(err <= tol)) {
+        ++bad;
+        if (shown < 6) { printf("   mismatch m=%d n=%d got=%g want=%g\n", m, n, got, acc); ++shown; }
+      }
+      if (c.act == HS_ACT_GELU) {
+        double ae = fabs(h2f(haux_out[(size_t)m * ldaux + n], c.bf) - pre);
+        if (ae > max_aux_err) max_aux_err = ae;
+        if (ae > (c.bf ? 2e-2 : 4e-3) * (1 + fabs(pre))) ++bad;
+      }
+    }
+  // pad columns of C (n in [N, ldc)) must be untouched
+  long pad_touched = 0;
+  for (int m = 0; m < M; ++m)
+    for (int n = N; n < ldc; ++n) {
+      float got;
+      if (c.out_f32) memcpy(&got, &hC[((size_t)m * ldc + n) * 4], 4);
+      else { uint16_t u; memcpy(&u, &hC[((size_t)m * ldc + n) * 2], 2); got = h2f(u, c.bf); }
+      if (got != c_init[(size_t)m * ldc + n]) ++pad_touched;
+    }
+  const bool ok = bad == 0 && pad_touched == 0;
+  printf("%s %-28s M=%d N=%d K=%d a_mn=%d b_mn=%d %s->%s max_err=%.3g aux_err=%.3g bad=%ld pad_touched=%ld\n",
+         ok ? "PASS" : "FAIL", c.name, M, N, K, c.a_mn, c.b_mn, c.bf ? "bf16" : "f16", c.out_f32 ? "f32" : "16b",
+         max_err, max_aux_err, bad, pad_touched);
+  cudaFree(dA); cudaFree(dB); cudaFree(dC); cudaFree(dbias); cudaFree(daux_in); cudaFree(daux_out);
+  return ok ? 0 : 1;
+}
+
+static void perf(const char* name, int M, int N, int K, int a_mn, int b_mn, int out_f32, int act, int bias) {
+  auto r8 = [](int x) { return (x + 7) / 8 * 8; };
+  const int lda = a_mn ? r8(M) : r8(K), ldb = b_mn ? r8(N) : r8(K), ldc = r8(N);
+  const size_t a_rows = a_mn ? K : M, b_rows = b_mn ? K : N;
+  void *dA, *dB, *dC, *dbias, *daux, *flush;
+  CK(cudaMalloc(&dA, a_rows * lda * 2)); CK(cudaMalloc(&dB, b_rows * ldb * 2));
+  CK(cudaMalloc(&dC, (size_t)M * ldc * 4)); CK(cudaMalloc(&dbias, N * 2)); CK(cudaMalloc(&daux, (size_t)M * ldc * 2));
+  const size_t flush_bytes = 256u << 20;
+  CK(cudaMalloc(&flush, flush_bytes));
+  CK(cudaMemset(dA, 0x11, a_rows * lda * 2)); CK(cudaMemset(dB, 0x11, b_rows * ldb * 2));
+  CK(cudaMemset(dC, 0, (size_t)M * ldc * 4)); CK(cudaMemset(dbias, 0, N * 2)); CK(cudaMemset(daux, 0, (size_t)M * ldc * 2));
+  hs_gemm_args g; memset(&g, 0, sizeof(g));
+  g.A = dA; g.B = dB; g.C = dC; g.M = M; g.N = N; g.K = K; g.lda = lda; g.ldb = ldb; g.ldc = ldc;
+  g.a_mn_major = a_mn; g.b_mn_major = b_mn; g.in_dtype = HS_BF16; g.out_dtype = out_f32 ? HS_F32 : HS_BF16;
+  g.bias = bias ? dbias : nullptr; g.act = act; g.aux_out = act == HS_ACT_GELU ? daux : nullptr;
+  g.aux_in = act == HS_ACT_DGELU_MUL ? daux : nullptr; g.ldaux = ldc; g.alpha = 1.0f;
+  cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+  for (int i = 0; i < 3; ++i) if (hs_gemm(&g, nullptr)) { printf("perf %s: %s\n", name, hs_last_error()); return; }
+  CK(cudaDeviceSynchronize());
+  float best = 1e30f, sum = 0; const int iters = 10;
+  for (int i = 0; i < iters; ++i) {
+    CK(cudaMemsetAsync(flush, i, flush_bytes));  // evict L2 between timed launches
+    CK(cudaEventRecord(e0));
+    hs_gemm(&g, nullptr);
+    CK(cudaEventRecord(e1));
+    CK(cudaEventSynchronize(e1));
+    float ms; CK(cudaEventElapsedTime(&ms, e0, e1));
+    best = ms < best ? ms : best; sum += ms;
+  }
+  const double fl = 2.0 * M * N * K;
+  printf("PERF %-26s M=%d N=%d K=%d a_mn=%d b_mn=%d out=%s act=%d  best %.3f ms (%.1f TFLOP/s)  mean %.3f ms (%.1f TFLOP/s)\n",
+         name, M, N, K, a_mn, b_mn, out_f32 ? "f32" : "bf16", act, best, fl / best * 1e-9, sum / iters,
+         fl / (sum / iters) * 1e-9);
+  cudaFree(dA); cudaFree(dB); cudaFree(dC); cudaFree(dbias); cudaFree(daux); cudaFree(flush);
+}
+
+int main(int argc, char** argv) {
+  const bool do_perf = !(argc > 1 && !strcmp(argv[1], "--no-perf"));
+  int fails = 0;
+  const Case cases[] = {
+      {128, 128, 64, 0, 0, 1, 0, 0, 0, 0, "tiny_kk"},
+      {128, 256, 128, 0, 0, 1, 0, 0, 0, 0, "one_tile_256"},
+      {256, 512, 256, 0, 0, 1, 0, 0, 0, 0, "kk_bf16"},
+      {256, 512, 256, 0, 0, 0, 0, 0, 0, 0, "kk_f16"},
+      {256, 512, 256, 0, 1, 1, 0, 0, 0, 0, "k_mn (dgrad)"},
+      {256, 512, 256, 1, 0, 1, 0, 0, 0, 0, "mn_k"},
+      {256, 512, 256, 1, 1, 1, 1, 0, 0, 0, "mn_mn f32 (wgrad)"},
+      {200, 264, 136, 0, 0, 1, 0, 1, 0, 0, "ragged kk bias"},
+      {200, 264, 136, 0, 1, 1, 0, 0, 0, 0, "ragged k_mn"},
+      {200, 264, 136, 1, 1, 1, 1, 0, 0, 1, "ragged mn_mn f32 accum"},
+      {32, 1024, 1024, 0, 0, 1, 0, 1, HS_ACT_TANH, 0, "pooler tanh"},
+      {384, 1024, 256, 0, 0, 1, 0, 1, HS_ACT_GELU, 0, "bias gelu + aux"},
+      {384, 1024, 256, 0, 0, 0, 0, 1, HS_ACT_GELU, 0, "bias gelu + aux f16"},
+      {384, 512, 1024, 0, 1, 1, 0, 0, HS_ACT_DGELU_MUL, 0, "dgrad * dgelu"},
+      {300, 30522, 128, 0, 0, 1, 0, 1, 0, 0, "decoder V=30522"},
+      {1024, 1024, 2048, 0, 0, 1, 0, 0, 0, 0, "multi-wave kk"},
+      {2048, 4096, 512, 1, 1, 1, 1, 0, 0, 0, "multi-wave mn_mn"},
+  };
+  for (const Case& c : cases) fails += run_case(c);
+  printf("SUMMARY: %d failing case(s)\n", fails);
+  if (do_perf) {
+    perf("qkv fwd", 4096, 3072, 1024, 0, 0, 0, 0, 1);
+    perf("attn-out fwd", 4096, 1024, 1024, 0, 0, 0, 0, 1);
+    perf("ffn1 fwd gelu", 4096, 4096, 1024, 0, 0, 0, HS_ACT_GELU, 1);
+    perf("ffn2 fwd", 4096, 1024, 4096, 0, 0, 0, 0, 1);
+    perf("ffn1 dgrad", 4096, 1024, 4096, 0, 1, 0, 0, 0);
+    perf("ffn2 dgrad dgelu", 4096, 4096, 1024, 0, 1, 0, HS_ACT_DGELU_MUL, 0);
+    perf("ffn1 wgrad f32", 4096, 1024, 4096, 1, 1, 1, 0, 0);
+    perf("ffn2 wgrad f32", 1024, 4096, 4096, 1, 1, 1, 0, 0);
+    perf("attn-out wgrad f32", 1024, 1024, 4096, 1, 1, 1, 0, 0);
+    perf("decoder 640 rows", 640, 30522, 1024, 0, 0, 0, 0, 1);
+    perf("square 8192", 8192, 8192, 8192, 0, 0, 0, 0, 0);
+    perf("square 8192 mn_mn", 8192, 8192, 8192, 1, 1, 0, 0, 0);
+  }
+  return fails ? 1 : 0;
+}
