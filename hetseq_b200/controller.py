@@ -1,0 +1,442 @@
+"""Controller: the training core (reference: controller.py:21-439).
+
+Same public surface as the reference -- ``train_step``, ``get_train_iterator``,
+``save_checkpoint``/``load_checkpoint``, ``lr_step``, ``get_meter``, lazy ``model`` / ``optimizer`` /
+``lr_scheduler`` properties -- over a different engine:
+
+* the model is never wrapped in DDP; its parameters are views into a ``FlatParamBuffer`` and a
+  data-parallel *backend* (parallel/data_parallel.py, parallel/fused_dp.py) turns the flat gradients
+  of all ranks into the update (bucket-wise, overlapped with backward);
+* gradient scaling, clipping and the optimizer update are one pass (optim/flat_optimizer.py);
+* per-step statistics stay on the device until ONE device->host read at the end of the step; the
+  reference synchronises mid-step (``.tolist()`` before ``multiply_grads``, controller.py:304) and the
+  slow stats path reads the byte buffer element by element (distributed_utils.py:120-122);
+* ``sample_size`` / ``nsentences`` / ``ntokens`` are real numbers;
+  ``--sample-size-mode reference`` restores the reference's gradient denominator;
+* dropout seeding keeps the resume contract ``seed + num_updates`` (controller.py:426-432) and
+  additionally folds in the rank so replicas draw different masks (Q14).
+"""
+from __future__ import annotations
+
+import contextlib
+import math
+import os
+from collections import OrderedDict
+from itertools import chain
+
+import torch
+
+from hetseq_b200 import registry
+from hetseq_b200.parallel import data_parallel, distributed_utils
+from hetseq_b200.parallel.flat_buffer import FlatParamBuffer
+from hetseq_b200.utils import checkpoint_utils
+from hetseq_b200.utils.meters import AverageMeter, CudaEventTimer, StopwatchMeter, TimeMeter
+
+
+class Controller(object):
+    """Synchronous data-parallel trainer for one model replica per process / GPU."""
+
+    def __init__(self, args, task, model, criterion=None, dummy_batch=None, oom_batch=None):
+        self.args = args
+        self.task = task
+
+        self.cuda = torch.cuda.is_available() and not args.cpu
+        self.device = torch.device('cuda', torch.cuda.current_device()) if self.cuda else torch.device('cpu')
+        if getattr(args, 'fp16', False):
+            model = model.half()
+        elif getattr(args, 'bf16', False):
+            model = model.bfloat16()
+        self._model = model.to(self.device)
+
+        self._dummy_batch = dummy_batch
+        self._oom_batch = oom_batch or dummy_batch
+        self._lr_scheduler = None
+        self._num_updates = 0
+        self._optim_history = None
+        self._optimizer = None
+        self._buffer = None
+        self._dp = None
+        self._prev_grad_norm = None
+        self._native_attached = False
+
+        self.fast_stat_sync = args.fast_stat_sync
+        self.step_timer = CudaEventTimer(use_cuda=self.cuda)
+        self.init_meters(args)
+
+    # -- meters -----------------------------------------------------------------------------------
+    def init_meters(self, args):
+        self.meters = OrderedDict()
+        self.meters['train_loss'] = AverageMeter()
+        self.meters['train_nll_loss'] = AverageMeter()
+        self.meters['valid_loss'] = AverageMeter()
+        self.meters['valid_nll_loss'] = AverageMeter()
+        self.meters['wps'] = TimeMeter()       # words per second
+        self.meters['ups'] = TimeMeter()       # updates per second
+        self.meters['wpb'] = AverageMeter()    # words per batch
+        self.meters['bsz'] = AverageMeter()    # sentences per batch
+        self.meters['gnorm'] = AverageMeter()  # gradient norm
+        self.meters['clip'] = AverageMeter()   # % of updates clipped
+        self.meters['oom'] = AverageMeter()    # out of memory (the reference looks this meter up but never creates it)
+        if getattr(args, 'fp16', False):
+            self.meters['loss_scale'] = AverageMeter()  # dynamic loss scale
+        self.meters['wall'] = TimeMeter()      # wall time in seconds
+        self.meters['train_wall'] = StopwatchMeter()  # train wall time in seconds
+
+    # -- lazily built engine ------------------------------------------------------------------------
+    @property
+    def model(self):
+        """The replica itself: there is no wrapper module (the reference returns a DDP wrapper)."""
+        if self._optimizer is None:
+            self._build_optimizer()
+        return self._model
+
+    @property
+    def optimizer(self):
+        if self._optimizer is None:
+            self._build_optimizer()
+        return self._optimizer
+
+    @property
+    def lr_scheduler(self):
+        if self._lr_scheduler is None:
+            self._build_optimizer()
+        return self._lr_scheduler
+
+    @property
+    def buffer(self) -> FlatParamBuffer:
+        if self._buffer is None:
+            self._build_optimizer()
+        return self._buffer
+
+    @property
+    def dp(self):
+        if self._dp is None:
+            self._build_optimizer()
+        return self._dp
+
+    def _trainable_params(self):
+        model = self._model
+        if hasattr(model, 'param_order'):
+            params = model.param_order()
+        else:
+            params = list(model.parameters())
+        return [p for p in params if p.requires_grad]
+
+    def _build_optimizer(self):
+        args = self.args
+        world = args.distributed_world_size if torch.distributed.is_initialized() else 1
+        rank = args.distributed_rank if world > 1 else 0
+
+        if self._buffer is None:
+            allocator = None
+            kind = getattr(args, 'dp_backend', 'auto')
+            if world > 1 and self.cuda and kind in ('auto', 'fused'):
+                from hetseq_b200.parallel import fused_dp
+                if kind == 'fused' or fused_dp.is_supported(args):
+                    allocator = fused_dp.symmetric_allocator(args)
+            canonical = [p for p in self._model.parameters() if p.requires_grad]
+            self._buffer = FlatParamBuffer(self._trainable_params(), world_size=world, rank=rank,
+                                           allocator=allocator)
+            pos = {id(p): i for i, p in enumerate(canonical)}
+            self._buffer.canonical_index = [pos[id(p)] for p in self._buffer.params]
+            self._dp = data_parallel.build_backend(args, self._buffer)
+            self._dp.broadcast_params()
+            self._attach_native()
+
+        self._optimizer = registry.lookup('optimizer', args.optimizer)(args, self._buffer, dp=self._dp)
+        # the LR scheduler is built right after the optimizer so that the initial LR is set
+        self._lr_scheduler = registry.lookup('lr_scheduler', args.lr_scheduler)(args, self._optimizer)
+        self._lr_scheduler.step_update(0)
+
+    def _attach_native(self):
+        """Swap the model's hot ops for the sm_100a kernels when running on a GPU."""
+        if self._native_attached:
+            return
+        self._native_attached = True
+        from hetseq_b200.ops import dispatch
+        if dispatch.use_native(self.args, self.device):
+            from hetseq_b200.ops import bert_native
+            bert_native.attach(self._model, self._buffer, self.args)
+
+    # -- checkpoints ------------------------------------------------------------------------------
+    def save_checkpoint(self, filename, extra_state):
+        """Write all training state to ``filename``. Every rank must call this when the optimizer
+        is sharded (state gathering is collective); only the master writes."""
+        extra_state['train_meters'] = self.meters
+        opt_state = None
+        if not self.args.no_save_optimizer_state:
+            if getattr(self.optimizer, 'sharded', False) or distributed_utils.is_master(self.args):
+                opt_state = self._buffer_to_canonical_order(self.optimizer.state_dict())
+        if distributed_utils.is_master(self.args):
+            state = checkpoint_utils.build_state(
+                self.args, self.get_model().state_dict(), self.optimizer.__class__.__name__, opt_state,
+                self.lr_scheduler.state_dict(), self.get_num_updates(), self._optim_history, extra_state)
+            checkpoint_utils.torch_persistent_save(state, filename)
+
+    def load_checkpoint(self, filename, reset_optimizer=False, reset_lr_scheduler=False,
+                        optimizer_overrides=None, reset_meters=False):
+        """Load all training state from a checkpoint file (every rank reads the file itself)."""
+        extra_state, self._optim_history, last_optim_state = None, [], None
+
+        if os.path.exists(filename):
+            state = checkpoint_utils.load_checkpoint_to_cpu(filename)
+            try:
+                self.get_model().load_state_dict(state['model'], strict=True)
+            except Exception:
+                raise Exception('Cannot load model parameters from checkpoint {}; please ensure that the '
+                                'architectures match.'.format(filename))
+            extra_state = state['extra_state']
+            self._optim_history = state['optimizer_history']
+            last_optim_state = state.get('last_optimizer_state', None)
+            if self._optimizer is not None:
+                self._optimizer.refresh_master()
+
+        if last_optim_state is not None and not reset_optimizer:
+            self._build_optimizer()   # rebuild after loading the model, params may have changed
+            last_optim = self._optim_history[-1]
+            assert last_optim['optimizer_name'] == self.optimizer.__class__.__name__, \
+                'Optimizer does not match; please reset the optimizer (--reset-optimizer).'
+            if not reset_lr_scheduler:
+                self.lr_scheduler.load_state_dict(last_optim['lr_scheduler_state'])
+            self.optimizer.load_state_dict(self._canonical_to_buffer_order(last_optim_state), optimizer_overrides)
+            self.set_num_updates(last_optim['num_updates'])
+
+        if extra_state is not None and 'train_iterator' in extra_state:
+            epoch = extra_state['train_iterator']['epoch']
+            print('| loaded checkpoint {} (epoch {} @ {} updates)'.format(filename, epoch, self.get_num_updates()))
+            self.lr_step(epoch)
+            if 'train_meters' in extra_state and not reset_meters:
+                self.meters.update(extra_state['train_meters'])
+                del extra_state['train_meters']
+                for meter in self.meters.values():
+                    if isinstance(meter, TimeMeter):
+                        meter.reset()
+        elif os.path.exists(filename):
+            # a file written by the reference itself: extra_state == {} (checkpoint_utils.py:204)
+            print('| loaded checkpoint {} without iterator state (@ {} updates)'.format(
+                filename, self.get_num_updates()))
+            extra_state = None
+        else:
+            print('| no existing checkpoint found {}'.format(filename))
+        return extra_state
+
+    def _buffer_to_canonical_order(self, opt_state):
+        canon = getattr(self.buffer, 'canonical_index', None)
+        if canon is None or canon == list(range(len(canon))):
+            return opt_state
+        out = dict(opt_state)
+        out['state'] = {canon[i]: v for i, v in opt_state.get('state', {}).items()}
+        out['state'] = dict(sorted(out['state'].items()))
+        return out
+
+    def _canonical_to_buffer_order(self, opt_state):
+        """Checkpoints index optimizer state by ``model.parameters()`` order (what a plain torch
+        optimizer would write); the flat buffer may order parameters differently."""
+        canon = getattr(self.buffer, 'canonical_index', None)
+        if canon is None or canon == list(range(len(canon))):
+            return opt_state
+        st = opt_state.get('state', {})
+        remapped = {}
+        for buf_i, can_i in enumerate(canon):
+            if can_i in st:
+                remapped[buf_i] = st[can_i]
+            elif str(can_i) in st:
+                remapped[buf_i] = st[str(can_i)]
+        out = dict(opt_state)
+        out['state'] = remapped
+        return out
+
+    # -- data -------------------------------------------------------------------------------------
+    def get_train_iterator(self, epoch, combine=True, load_dataset=True):
+        if load_dataset:
+            print('| loading train data for epoch {}'.format(epoch))
+            self.task.load_dataset(self.args.train_subset)
+        return self.task.get_batch_iterator(
+            dataset=self.task.dataset(self.args.train_subset),
+            max_tokens=self.args.max_tokens, max_sentences=self.args.max_sentences, max_positions=None,
+            ignore_invalid_inputs=True,
+            required_batch_size_multiple=self.args.required_batch_size_multiple,
+            seed=self.args.seed, num_shards=self.args.distributed_world_size,
+            shard_id=self.args.distributed_rank, num_workers=self.args.num_workers, epoch=epoch)
+
+    # -- the hot loop -------------------------------------------------------------------------------
+    def train_step(self, samples, dummy_batch=False, raise_oom=False):
+        """forward / backward over the micro-batches of one update, then reduce, clip and step."""
+        if self._dummy_batch is None:
+            self._dummy_batch = samples[0]
+
+        self._set_seed()
+        model = self.model
+        model.train()
+        self.zero_grad()
+        dp, opt = self.dp, self.optimizer
+
+        if not dummy_batch:
+            self.meters['train_wall'].start()
+            self.step_timer.start()
+
+        # host-side integer stats + device-side loss sum; nothing here synchronises
+        n_sample_size = n_sentences = n_tokens = 0
+        loss_sum = torch.zeros((), dtype=torch.float32, device=self.device)
+        logging_outputs, ooms = [], 0
+        dp.begin_update(len(samples))
+        for i, sample in enumerate(samples):
+            prepared = self._prepare_sample(sample)
+            if prepared is None:
+                # uneven shards: run on the cached dummy batch and ignore its gradients so that
+                # every rank still takes part in the reduction (controller.py:237-241)
+                prepared = self._prepare_sample(self._dummy_batch)
+                ignore_grad = True
+            else:
+                ignore_grad = False
+            sample_dev, stats = prepared
+            dp.begin_micro_batch(i, is_last=(i == len(samples) - 1))
+            try:
+                loss, sample_size, logging_output = self.task.train_step(
+                    sample_dev, model, opt, ignore_grad, stats=stats)
+            except RuntimeError as e:
+                if 'out of memory' in str(e):
+                    raise RuntimeError('ran out of memory with exception') from e
+                raise
+            if not ignore_grad:
+                logging_outputs.append(logging_output)
+                n_sample_size += sample_size
+                n_sentences += logging_output.get('nsentences', 0)
+                n_tokens += logging_output.get('ntokens', 0)
+                weight = logging_output.get('nsentences', 1) if self.args.sample_size_mode == 'batch' else 1.0
+                loss_sum = loss_sum + logging_output['loss'].float() * weight
+
+        if dummy_batch:
+            return None
+
+        dp.finish_gradients(opt)
+
+        # ---- stats: [sample_size, nsentences, loss, nll_loss, ntokens, ooms] like controller.py:292-314
+        stats_vec = torch.zeros(6, dtype=torch.float64, device=self.device)
+        stats_vec[0], stats_vec[1], stats_vec[4], stats_vec[5] = n_sample_size, n_sentences, n_tokens, ooms
+        stats_vec[2] = loss_sum.double()
+        stats_vec[3] = loss_sum.double()
+        if self._sync_stats():
+            if self.fast_stat_sync:
+                comm = stats_vec if stats_vec.device == distributed_utils.comm_device() else stats_vec.cpu()
+                torch.distributed.all_reduce(comm)
+                stats_vec = comm.to(self.device)
+            else:
+                # general path: gather every rank's logging outputs, aggregate them (the reference
+                # gathers and then forgets to aggregate, controller.py:315-334), and run the
+                # cross-rank gradient-norm consistency check on the previous step's norm
+                host = stats_vec.tolist()
+                gathered = distributed_utils.all_gather_list([host, self._prev_grad_norm])
+                prev_norms = [g[1] for g in gathered]
+                assert (all(n == prev_norms[0] for n in prev_norms)
+                        or all(n is None or math.isnan(n) or math.isinf(n) for n in prev_norms)), \
+                    'Fatal error: gradients are inconsistent between workers'
+                stats_vec = torch.tensor([sum(g[0][k] for g in gathered) for k in range(6)],
+                                         dtype=torch.float64, device=self.device)
+
+        logging_output = None
+        try:
+            sample_size_dev = stats_vec[0]
+            # normalise grads by sample size (controller.py:338-339); the backend already made them
+            # the mean over ranks, so the factor is world / sample_size like the reference's
+            world = float(self.args.distributed_world_size if self._sync_stats() else 1)
+            opt.multiply_grads(torch.where(sample_size_dev > 0, world / sample_size_dev.clamp(min=1e-12),
+                                           torch.ones_like(sample_size_dev)).float())
+            grad_norm = opt.clip_grad_norm(self.args.clip_norm)
+            opt.step()
+            self.set_num_updates(self.get_num_updates() + 1)
+            self.task.update_step(self._num_updates)
+
+            # ---- the single device->host read of the step
+            readback = torch.cat([stats_vec, grad_norm.detach().double().reshape(1)]).tolist()
+            sample_size, nsentences, loss_total, nll_total, ntokens, ooms, gnorm = readback
+            self._prev_grad_norm = gnorm
+            # like the fast path of the reference (controller.py:299-304) losses are logged as
+            # sum / (sample_size * ln 2); in 'batch' mode the sum is weighted by sentences so this is
+            # the true per-sentence mean in base 2
+            denom = max(sample_size, 1e-12) * math.log(2)
+            loss_avg = loss_total / denom
+            logging_output = {'loss': loss_avg, 'nll_loss': nll_total / denom,
+                              'ntokens': ntokens, 'nsentences': nsentences, 'sample_size': sample_size}
+
+            self.meters['wps'].update(ntokens)
+            self.meters['ups'].update(1.)
+            self.meters['wpb'].update(ntokens)
+            self.meters['bsz'].update(nsentences)
+            self.meters['gnorm'].update(gnorm)
+            self.meters['clip'].update(1. if gnorm > self.args.clip_norm and self.args.clip_norm > 0 else 0.)
+            self.meters['oom'].update(ooms)
+            self.meters['train_loss'].update(loss_avg, sample_size)
+            if 'loss_scale' in self.meters:
+                self.meters['loss_scale'].reset()
+                self.meters['loss_scale'].update(opt.loss_scale)
+        except OverflowError as e:
+            print('| WARNING: overflow detected, ' + str(e))
+            self.zero_grad()
+            logging_output = None
+
+        self.step_timer.stop()
+        self.meters['train_wall'].stop()
+        return logging_output
+
+    def valid_step(self, sample):
+        """Forward only (the reference never validates: train.py:93; available via --enable-validation)."""
+        prepared = self._prepare_sample(sample)
+        if prepared is None:
+            return None
+        sample_dev, _ = prepared
+        loss, sample_size, logging_output = self.task.valid_step(sample_dev, self._model)
+        return float(loss), sample_size, logging_output
+
+    def zero_grad(self):
+        self.optimizer.zero_grad()
+
+    def lr_step(self, epoch, val_loss=None):
+        self.lr_scheduler.step(epoch, val_loss)
+        return self.lr_step_update()
+
+    def lr_step_update(self):
+        return self.lr_scheduler.step_update(self.get_num_updates())
+
+    def get_lr(self):
+        return self.optimizer.get_lr()
+
+    def get_model(self):
+        return self._model
+
+    def get_meter(self, name):
+        if name not in self.meters:
+            return None
+        return self.meters[name]
+
+    def get_num_updates(self):
+        return self._num_updates
+
+    def set_num_updates(self, num_updates):
+        self._num_updates = num_updates
+        self.lr_step_update()
+
+    def _prepare_sample(self, sample):
+        """Returns (device sample, host stats) or None for an empty (padding) batch."""
+        if sample is None or len(sample) == 0:
+            return None
+        stats = self.task.sample_stats(sample)
+        return self.task.prepare_sample(sample, self.device), stats
+
+    def _set_seed(self):
+        """seed + num_updates keeps results reproducible across resume (controller.py:426-432);
+        the rank offset gives every replica its own dropout stream."""
+        seed = self.args.seed + self.get_num_updates()
+        rank = self.args.distributed_rank if self._sync_stats() else 0
+        torch.manual_seed(seed + 1000003 * rank)
+        if self.cuda:
+            torch.cuda.manual_seed(seed + 1000003 * rank)
+        from hetseq_b200.ops import rng
+        rng.set_step_seed(seed, rank)
+
+    def _sync_stats(self):
+        return self.args.distributed_world_size > 1 and torch.distributed.is_initialized()
+
+    def close(self):
+        if self._dp is not None:
+            self._dp.close()

@@ -1,0 +1,262 @@
+"""Resumable, epoch- and shard-aware iterators (reference: data/iterators.py).
+
+Same public classes and state contract as the reference --
+``EpochBatchIterator.state_dict() == {'epoch', 'iterations_in_epoch'}``, per-epoch batch shuffle
+seeded with ``seed + epoch`` identically on every rank, round-robin sharding padded with empty
+batches so every rank takes the same number of steps -- built on an index plan (numpy arrays)
+instead of lists of lists, plus a pinned-memory prefetch thread for the host->device hand-off
+(SURVEY.md W13).
+"""
+from __future__ import annotations
+
+import itertools
+import math
+import os
+import queue
+import threading
+from typing import Optional
+
+import numpy as np
+import torch
+
+from hetseq_b200.data import data_utils
+
+
+class CountingIterator(object):
+    """Iterator wrapper that counts consumed elements (data/iterators.py:10-42)."""
+
+    def __init__(self, iterable, start=0, length=None):
+        self.iterable = iterable
+        self.count = start
+        self.itr = iter(self)
+        self.len = start + (len(iterable) if length is None else length)
+
+    def __len__(self):
+        return self.len
+
+    def __iter__(self):
+        for x in self.iterable:
+            self.count += 1
+            yield x
+
+    def __next__(self):
+        return next(self.itr)
+
+    def has_next(self):
+        return self.count < len(self)
+
+    def skip(self, num_to_skip):
+        next(itertools.islice(self.itr, num_to_skip, num_to_skip), None)
+        return self
+
+
+class _BatchLoader(object):
+    """Turns a list of index batches into collated samples; optional DataLoader workers."""
+
+    def __init__(self, dataset, collate_fn, batches, num_workers=0):
+        self.dataset, self.collate_fn, self.batches, self.num_workers = dataset, collate_fn, batches, num_workers
+
+    def __len__(self):
+        return len(self.batches)
+
+    def __iter__(self):
+        if self.num_workers > 0:
+            os.environ['PYTHONWARNINGS'] = 'ignore:semaphore_tracker:UserWarning'
+            yield from torch.utils.data.DataLoader(
+                self.dataset, collate_fn=self.collate_fn,
+                batch_sampler=[list(map(int, b)) for b in self.batches], num_workers=self.num_workers)
+            return
+        fetch_batch = getattr(self.dataset, 'fetch_batch', None)
+        for b in self.batches:
+            if fetch_batch is not None:
+                yield fetch_batch(b)           # vectorised path: dataset builds the whole batch
+            else:
+                yield self.collate_fn([self.dataset[int(i)] for i in b])
+
+
+class EpochBatchIterator(object):
+    """Multi-epoch iterator over a dataset with frozen batches (data/iterators.py:67-211)."""
+
+    def __init__(self, dataset, collate_fn, batch_sampler, seed=1, num_shards=1, shard_id=0,
+                 num_workers=0, epoch=0):
+        self.dataset = dataset
+        self.collate_fn = collate_fn
+        if isinstance(batch_sampler, data_utils.BatchPlan):
+            self.frozen_batches = batch_sampler
+        else:
+            self.frozen_batches = tuple(batch_sampler)
+        self.seed = seed
+        self.num_shards = num_shards
+        self.shard_id = shard_id
+        self.num_workers = num_workers
+        self.epoch = epoch
+        self._cur_epoch_itr = None
+        self._next_epoch_itr = None
+
+    def __len__(self):
+        return len(self.frozen_batches)
+
+    def next_epoch_itr(self, shuffle=True, fix_batches_to_gpus=False):
+        if self._next_epoch_itr is not None:
+            self._cur_epoch_itr = self._next_epoch_itr
+            self._next_epoch_itr = None
+        else:
+            self.epoch += 1
+            self._cur_epoch_itr = self._get_iterator_for_epoch(
+                self.epoch, shuffle, fix_batches_to_gpus=fix_batches_to_gpus)
+        if hasattr(self.dataset, 'set_epoch'):
+            self.dataset.set_epoch(self.epoch)
+        return self._cur_epoch_itr
+
+    def end_of_epoch(self) -> bool:
+        return not self._cur_epoch_itr.has_next()
+
+    @property
+    def iterations_in_epoch(self):
+        if self._cur_epoch_itr is not None:
+            return self._cur_epoch_itr.count
+        if self._next_epoch_itr is not None:
+            return self._next_epoch_itr.count
+        return 0
+
+    def state_dict(self):
+        return {'epoch': self.epoch, 'iterations_in_epoch': self.iterations_in_epoch}
+
+    def load_state_dict(self, state_dict):
+        self.epoch = state_dict['epoch']
+        itr_pos = state_dict.get('iterations_in_epoch', 0)
+        if itr_pos > 0:
+            # fast-forward inside the epoch; a finished epoch yields None and the next
+            # next_epoch_itr() call simply starts epoch+1
+            self._next_epoch_itr = self._get_iterator_for_epoch(
+                self.epoch, shuffle=state_dict.get('shuffle', True), offset=itr_pos)
+
+    def epoch_batch_ids(self, epoch, shuffle=True, fix_batches_to_gpus=False) -> np.ndarray:
+        """Batch ids this shard visits in ``epoch`` (-1 = padding batch)."""
+        n = len(self.frozen_batches)
+        order = None
+        if shuffle and not fix_batches_to_gpus:
+            order = np.arange(n, dtype=np.int64)
+            with data_utils.numpy_seed(self.seed + epoch):
+                np.random.shuffle(order)
+        ids = data_utils.shard_plan(order, n, self.num_shards, self.shard_id)
+        if shuffle and fix_batches_to_gpus:
+            with data_utils.numpy_seed(self.seed + epoch + self.shard_id):
+                np.random.shuffle(ids)
+        return ids
+
+    def _get_iterator_for_epoch(self, epoch, shuffle, fix_batches_to_gpus=False, offset=0):
+        ids = self.epoch_batch_ids(epoch, shuffle, fix_batches_to_gpus)
+        if offset > 0 and offset >= len(ids):
+            return None
+        empty = np.empty(0, dtype=np.int64)
+        batches = [self.frozen_batches[int(b)] if b >= 0 else empty for b in ids[offset:]]
+        return CountingIterator(_BatchLoader(self.dataset, self.collate_fn, batches, self.num_workers),
+                                start=offset)
+
+
+class GroupedIterator(object):
+    """Chunks of ``chunk_size`` consecutive items (one chunk = one optimizer update)."""
+
+    def __init__(self, iterable, chunk_size):
+        self._len = int(math.ceil(len(iterable) / float(chunk_size)))
+        self.offset = int(math.ceil(getattr(iterable, 'count', 0) / float(chunk_size)))
+        self.itr = iterable
+        self.chunk_size = chunk_size
+
+    def __len__(self):
+        return self._len
+
+    def __iter__(self):
+        return self
+
+    def __next__(self):
+        chunk = []
+        try:
+            for _ in range(self.chunk_size):
+                chunk.append(next(self.itr))
+        except StopIteration as e:
+            if len(chunk) == 0:
+                raise e
+        return chunk
+
+
+class ShardedIterator(object):
+    """Every ``num_shards``-th element starting at ``shard_id``, padded to ceil(N / num_shards)."""
+
+    def __init__(self, iterable, num_shards, shard_id, fill_value=None):
+        if shard_id < 0 or shard_id >= num_shards:
+            raise ValueError('shard_id must be between 0 and num_shards')
+        self._sharded_len = len(iterable) // num_shards
+        if len(iterable) % num_shards > 0:
+            self._sharded_len += 1
+        self.itr = itertools.zip_longest(
+            range(self._sharded_len),
+            itertools.islice(iterable, shard_id, len(iterable), num_shards),
+            fillvalue=fill_value)
+
+    def __len__(self):
+        return self._sharded_len
+
+    def __iter__(self):
+        return self
+
+    def __next__(self):
+        return next(self.itr)[1]
+
+
+class PrefetchIterator(object):
+    """Runs the wrapped iterator in a background thread, ``depth`` items ahead, pinning CPU tensors
+    so the trainer's host->device copies are asynchronous (the reference copies synchronously from
+    pageable memory, utils.py:32-37). ``len`` / ``count`` / ``offset`` are forwarded so it can sit
+    between CountingIterator and GroupedIterator or wrap a GroupedIterator."""
+
+    _END = object()
+
+    def __init__(self, iterable, depth=2, pin_memory: Optional[bool] = None):
+        self.iterable = iterable
+        self.pin = torch.cuda.is_available() if pin_memory is None else pin_memory
+        self.q: queue.Queue = queue.Queue(maxsize=max(1, depth))
+        self._err = None
+        self.offset = getattr(iterable, 'offset', 0)
+        self._thread = threading.Thread(target=self._worker, daemon=True)
+        self._started = False
+
+    def __len__(self):
+        return len(self.iterable)
+
+    @property
+    def count(self):
+        return getattr(self.iterable, 'count', 0)
+
+    def _pin(self, x):
+        if torch.is_tensor(x):
+            return x.pin_memory() if (x.device.type == 'cpu' and not x.is_pinned()) else x
+        if isinstance(x, dict):
+            return {k: self._pin(v) for k, v in x.items()}
+        if isinstance(x, (list, tuple)):
+            return type(x)(self._pin(v) for v in x)
+        return x
+
+    def _worker(self):
+        try:
+            for item in self.iterable:
+                self.q.put(self._pin(item) if self.pin else item)
+        except BaseException as e:  # surfaced in the consumer thread
+            self._err = e
+        finally:
+            self.q.put(self._END)
+
+    def __iter__(self):
+        return self
+
+    def __next__(self):
+        if not self._started:
+            self._started = True
+            self._thread.start()
+        item = self.q.get()
+        if item is self._END:
+            if self._err is not None:
+                raise self._err
+            raise StopIteration
+        return item

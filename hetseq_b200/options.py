@@ -150,11 +150,12 @@ def add_distributed_training_args(parser):
                        help='do not spawn multiple processes even if multiple GPUs are visible')
     group.add_argument('--ddp-backend', default='c10d', type=str, choices=['c10d'],
                        help='accepted for compatibility; see --dp-backend')
-    group.add_argument('--dp-backend', default='auto', choices=['auto', 'fused', 'nccl'],
+    group.add_argument('--dp-backend', default='auto', choices=['auto', 'fused', 'nccl', 'sharded'],
                        help="gradient path. 'fused': in-kernel reduce-scatter over NVLink peer memory + "
                             "clip/unscale + sharded Adam + all-gather (no NCCL call); 'nccl': bucketed "
-                            "all-reduce + replicated optimizer (the baseline); 'auto': fused when the "
-                            "ranks share one NVLink domain and CUDA, else nccl")
+                            "all-reduce + replicated optimizer (the baseline); 'sharded': the fused protocol "
+                            "emulated with torch.distributed collectives (CPU tests); 'auto': fused when "
+                            "the ranks share one NVLink domain and CUDA, else nccl")
     group.add_argument('--bucket-cap-mb', default=25, type=int, metavar='MB',
                        help='bucket size for reduction')
     group.add_argument('--fix-batches-to-gpus', action='store_true',

@@ -1,0 +1,180 @@
+"""Data-parallel gradient backends over a FlatParamBuffer.
+
+The reference wraps the model in ``torch.nn.parallel.DistributedDataParallel`` (controller.py:74-89)
+and skips the all-reduce on all but the last micro-batch with ``no_sync()`` (controller.py:245-258).
+Here the model is never wrapped. A backend owns the question "how do the flat gradients of W ranks
+become an update of the flat parameters":
+
+``LocalBackend``       world size 1 -- nothing to do.
+``AllReduceBackend``   the in-framework baseline (``--dp-backend nccl``): bucketed asynchronous
+                       all-reduce of the flat gradient over torch.distributed (NCCL on GPUs, Gloo in
+                       CPU tests), launched bucket by bucket from gradient-ready callbacks so it
+                       overlaps with backward, followed by a replicated (unsharded) update. This is
+                       what DDP + the reference's optimizer loop amount to, minus the launches.
+``FusedBackend``       the product (``--dp-backend fused``, parallel/fused_dp.py): in-kernel
+                       reduce-scatter over NVLink peer memory, sharded update, in-kernel all-gather.
+
+Common protocol, driven by the Controller for each optimizer update:
+    begin_update(n_micro) -> [micro-batch backward passes; ready callbacks fire on the last one]
+    -> finish_gradients() -> optimizer.clip_grad_norm()/step() -> (sharded: all_gather_params)
+Gradient semantics match DDP: after ``finish_gradients`` the optimizer sees the MEAN over ranks
+(the 1/W is folded into the optimizer's pending multiplier, no extra pass over memory).
+"""
+from __future__ import annotations
+
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+from hetseq_b200.parallel.flat_buffer import FlatParamBuffer
+
+
+class LocalBackend(object):
+    sharded = False
+    name = 'local'
+
+    def __init__(self, args, buffer: FlatParamBuffer):
+        self.args, self.buffer = args, buffer
+        self.world_size, self.rank = 1, 0
+
+    def broadcast_params(self):
+        pass
+
+    def begin_update(self, num_micro_batches: int):
+        pass
+
+    def begin_micro_batch(self, index: int, is_last: bool):
+        pass
+
+    def finish_gradients(self, optimizer):
+        pass
+
+    def all_reduce_scalar(self, t: torch.Tensor) -> torch.Tensor:
+        return t
+
+    def check_params_consistent(self) -> bool:
+        return True
+
+    def close(self):
+        pass
+
+
+class AllReduceBackend(LocalBackend):
+    """Bucketed all-reduce of the flat gradient + replicated optimizer (the NCCL baseline)."""
+
+    name = 'nccl'
+
+    def __init__(self, args, buffer: FlatParamBuffer, group=None):
+        super().__init__(args, buffer)
+        self.group = group
+        self.world_size = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        elem = buffer.flat_grad.element_size()
+        self.buckets = buffer.bucket_ranges(int(getattr(args, 'bucket_cap_mb', 25)) * (1 << 20) // elem)
+        # bucket -> parameters that must be ready before it can be reduced
+        self._bucket_params = [buffer.params_in_range(s, e) for s, e in self.buckets]
+        self._param_buckets: List[List[int]] = [[] for _ in buffer.params]
+        for b, plist in enumerate(self._bucket_params):
+            for i in plist:
+                self._param_buckets[i].append(b)
+        self._pending = [0] * len(self.buckets)
+        self._launched = [False] * len(self.buckets)
+        self._handles = []
+        self._armed = False
+        buffer.ready_callback = self._on_param_ready
+
+    def broadcast_params(self):
+        """Rank 0's parameters become everybody's (what the DDP constructor does)."""
+        dist.broadcast(self.buffer.flat_param, src=0, group=self.group)
+
+    def begin_update(self, num_micro_batches: int):
+        self._handles = []
+
+    def begin_micro_batch(self, index: int, is_last: bool):
+        self._armed = bool(is_last)
+        if is_last:
+            self._pending = [len(p) for p in self._bucket_params]
+            self._launched = [False] * len(self.buckets)
+
+    def _launch(self, b: int):
+        s, e = self.buckets[b]
+        self._launched[b] = True
+        self._handles.append(dist.all_reduce(self.buffer.flat_grad[s:e], group=self.group, async_op=True))
+
+    def _on_param_ready(self, i: int):
+        """Called (from autograd hooks or native ops) when parameter i's gradient is final."""
+        if not self._armed:
+            return
+        for b in self._param_buckets[i]:
+            self._pending[b] -= 1
+            if self._pending[b] == 0 and not self._launched[b]:
+                self._launch(b)
+
+    def finish_gradients(self, optimizer):
+        # buckets whose parameters never reported (unused parameters, or a model without hooks)
+        for b in range(len(self.buckets)):
+            if not self._launched[b]:
+                self._launch(b)
+        for h in self._handles:
+            h.wait()
+        self._handles = []
+        self._armed = False
+        optimizer.multiply_grads(1.0 / self.world_size)
+
+    def all_reduce_scalar(self, t: torch.Tensor) -> torch.Tensor:
+        t = t.clone()
+        dist.all_reduce(t, group=self.group)
+        return t
+
+    def check_params_consistent(self) -> bool:
+        """Cross-rank invariant replacing the reference's grad-norm equality assert
+        (controller.py:325-328): every replica must hold bit-identical parameters."""
+        p = self.buffer.flat_param
+        chk = torch.stack([p.float().sum(), p.float().abs().sum()]).to(torch.float64)
+        lo, hi = chk.clone(), chk.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN, group=self.group)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=self.group)
+        return bool(torch.equal(lo, hi))
+
+
+class ShardedAllReduceBackend(AllReduceBackend):
+    """Reference implementation of the *sharded* protocol on top of torch.distributed collectives
+    (reduce = all-reduce, gather = all-gather of compact shards). Used by the CPU/Gloo tests to
+    exercise the partitioned optimizer and checkpoint gathering without GPUs; the fused NVLink
+    backend implements the same interface with in-kernel transfers."""
+
+    sharded = True
+    name = 'sharded-allreduce'
+
+    def all_gather_compact(self, compact: torch.Tensor) -> torch.Tensor:
+        """[shard_size] per rank -> [world, shard_size]."""
+        compact = compact.contiguous()
+        out = [torch.empty_like(compact) for _ in range(self.world_size)]
+        dist.all_gather(out, compact, group=self.group)
+        return torch.stack(out)
+
+    def all_gather_params(self, buffer: FlatParamBuffer):
+        mine = buffer.owned(buffer.flat_param).reshape(-1).contiguous()
+        full = self.all_gather_compact(mine)
+        buffer.flat_param.copy_(buffer.compact_to_flat(full))
+
+
+def build_backend(args, buffer: FlatParamBuffer):
+    """Pick the gradient backend for this run (``--dp-backend``)."""
+    world = getattr(args, 'distributed_world_size', 1)
+    if world <= 1 or not dist.is_initialized():
+        return LocalBackend(args, buffer)
+    choice = getattr(args, 'dp_backend', 'auto')
+    on_cuda = buffer.device.type == 'cuda'
+    if choice == 'auto':
+        from hetseq_b200.parallel import fused_dp
+        choice = 'fused' if (on_cuda and fused_dp.is_supported(args)) else 'nccl'
+    if choice == 'fused':
+        if not on_cuda:
+            raise RuntimeError('--dp-backend fused needs CUDA devices in one NVLink domain')
+        from hetseq_b200.parallel import fused_dp
+        return fused_dp.FusedBackend(args, buffer)
+    if choice == 'sharded':
+        return ShardedAllReduceBackend(args, buffer)
+    return AllReduceBackend(args, buffer)

@@ -1,0 +1,185 @@
+"""Flat parameter / gradient buffers.
+
+The reference never flattens anything: it relies on DDP's internal 25 MiB buckets for the gradient
+all-reduce (controller.py:78-86, options.py:122) and loops over tensors for ``multiply_grads``,
+``clip_grad_norm`` and ``Adam.step`` (optim.py:59-70,162-231) -- thousands of tiny launches per
+step. Here every trainable parameter is a *view* into one contiguous buffer
+and so is its gradient ("main grad"), which makes the gradient path a handful of kernels over
+flat memory: one norm, one fused unscale/clip/Adam, and -- in the fused data-parallel backend --
+reduce-scatter / all-gather over rank-contiguous shards of the very same buffers.
+
+Layout: parameters in registration order, each start aligned to ``ALIGN`` elements, total length
+padded to a multiple of ``world_size * CHUNK``. Ownership for the sharded optimizer is *cyclic by
+chunk*: element ``i`` belongs to rank ``(i // CHUNK) % world_size``. Any bucket whose bounds are
+multiples of ``world_size * CHUNK`` is therefore spread evenly over all ranks, so a bucket-wise
+reduce-scatter loads every GPU's NVLink ingress equally no matter how buckets are chosen. A rank's
+optimizer state is compact (``total / world_size`` elements); ``owned(t)`` gives the strided view
+of a flat tensor that corresponds to it. Tied parameters (one ``nn.Parameter`` reachable
+through several modules, e.g. BERT's decoder/word-embedding weight, bert_modeling.py:541) appear
+once.
+"""
+from __future__ import annotations
+
+from typing import Callable, Iterable, List, Optional, Tuple
+
+import torch
+
+ALIGN = 128    # elements; 256 B for 16-bit params, 512 B for fp32
+CHUNK = 2048   # elements; ownership granule of the sharded optimizer (8 KiB of fp32 gradient)
+
+
+def _round_up(x: int, m: int) -> int:
+    return (x + m - 1) // m * m
+
+
+class FlatParamBuffer(object):
+    """Owns ``flat_param`` (model dtype) and ``flat_grad`` (``grad_dtype``, fp32 by default).
+
+    After construction ``p.data`` of every parameter aliases ``flat_param`` and ``p.main_grad``
+    aliases ``flat_grad``. Gradients reach ``main_grad`` in one of three ways:
+
+    * native fused ops write (or accumulate) it directly and return no autograd gradient;
+    * parameters whose dtype equals ``grad_dtype`` get ``p.grad = p.main_grad`` so autograd
+      accumulates in place;
+    * any other parameter gets a post-accumulate hook that folds ``p.grad`` into ``main_grad``.
+    """
+
+    def __init__(self, params: Iterable[torch.nn.Parameter], world_size: int = 1, rank: int = 0,
+                 grad_dtype: torch.dtype = torch.float32,
+                 allocator: Optional[Callable[[int, torch.dtype, torch.device], torch.Tensor]] = None):
+        seen = set()
+        self.params: List[torch.nn.Parameter] = []
+        for p in params:
+            if p.requires_grad and id(p) not in seen:
+                seen.add(id(p))
+                self.params.append(p)
+        if not self.params:
+            raise ValueError('FlatParamBuffer needs at least one trainable parameter')
+        p0 = self.params[0]
+        self.device, self.param_dtype = p0.device, p0.dtype
+        for p in self.params:
+            if p.device != self.device or p.dtype != self.param_dtype:
+                raise ValueError('all parameters must share one device and dtype '
+                                 f'(got {p.device}/{p.dtype} vs {self.device}/{self.param_dtype})')
+        self.grad_dtype = grad_dtype
+        self.world_size, self.rank = int(world_size), int(rank)
+
+        self.offsets: List[int] = []
+        self.numels: List[int] = []
+        off = 0
+        for p in self.params:
+            self.offsets.append(off)
+            self.numels.append(p.numel())
+            off = _round_up(off + p.numel(), ALIGN)
+        self.used = off
+        self.total = _round_up(max(off, 1), self.world_size * CHUNK)
+        self.shard_size = self.total // self.world_size
+        self.num_blocks = self.total // (self.world_size * CHUNK)
+
+        alloc = allocator or (lambda n, dt, dev: torch.zeros(n, dtype=dt, device=dev))
+        self.flat_param = alloc(self.total, self.param_dtype, self.device)
+        self.flat_grad = alloc(self.total, self.grad_dtype, self.device)
+        self.main_grads: List[torch.Tensor] = []
+        self._written: List[bool] = [False] * len(self.params)
+        self._hooks = []
+        with torch.no_grad():
+            for i, p in enumerate(self.params):
+                view = self.flat_param[self.offsets[i]: self.offsets[i] + self.numels[i]].view(p.shape)
+                view.copy_(p.data)
+                p.data = view
+                g = self.flat_grad[self.offsets[i]: self.offsets[i] + self.numels[i]].view(p.shape)
+                self.main_grads.append(g)
+                p.main_grad = g
+                p._hs_flat = (self, i)
+                self._hooks.append(p.register_post_accumulate_grad_hook(self._make_hook(i)))
+        #: called with a parameter index once that parameter's gradient is final for the current
+        #: micro-batch; data-parallel backends use it to start reducing a bucket during backward
+        self.ready_callback: Optional[Callable[[int], None]] = None
+        self.zero_grad()
+
+    # -- gradient plumbing ----------------------------------------------------------------------
+    def _make_hook(self, i: int):
+        fold = self.param_dtype != self.grad_dtype
+
+        def hook(p):
+            if fold and p.grad is not None:
+                g = self.main_grads[i]
+                if self._written[i]:
+                    g.add_(p.grad)
+                else:
+                    g.copy_(p.grad)
+                    self._written[i] = True
+                p.grad = None
+            if self.ready_callback is not None:
+                self.ready_callback(i)
+        return hook
+
+    def notify_ready(self, p: torch.nn.Parameter) -> None:
+        """For ops that wrote ``main_grad`` themselves (no autograd hook fires for them)."""
+        if self.ready_callback is not None:
+            self.ready_callback(p._hs_flat[1])
+
+    def grad_target(self, p: torch.nn.Parameter) -> Tuple[torch.Tensor, bool]:
+        """(main_grad view, accumulate?) for an op that writes the gradient itself."""
+        i = p._hs_flat[1]
+        acc = self._written[i]
+        self._written[i] = True
+        return self.main_grads[i], acc
+
+    def ensure_initialized(self, p: torch.nn.Parameter) -> torch.Tensor:
+        """main_grad view guaranteed to hold a valid partial sum (for ops that can only accumulate)."""
+        i = p._hs_flat[1]
+        if not self._written[i]:
+            self.main_grads[i].zero_()
+            self._written[i] = True
+        return self.main_grads[i]
+
+    def zero_grad(self, set_to_zero: bool = True) -> None:
+        """Start a new accumulation window.
+
+        With ``set_to_zero`` the whole flat gradient is cleared with one memset. Native ops do not
+        need that (their first write in a window overwrites), so the trainer passes ``False`` when
+        every parameter is produced by such an op.
+        """
+        if set_to_zero:
+            self.flat_grad.zero_()
+        same = self.param_dtype == self.grad_dtype
+        for i, p in enumerate(self.params):
+            # after a memset every view is a valid partial sum, so later writes must accumulate
+            self._written[i] = bool(set_to_zero)
+            p.grad = self.main_grads[i] if same else None
+
+    def mark_all_written(self) -> None:
+        for i in range(len(self._written)):
+            self._written[i] = True
+
+    # -- shards ---------------------------------------------------------------------------------
+    def owned(self, flat: torch.Tensor, rank: Optional[int] = None) -> torch.Tensor:
+        """[num_blocks, CHUNK] strided view of the elements of ``flat`` that ``rank`` owns."""
+        r = self.rank if rank is None else rank
+        return flat.view(self.num_blocks, self.world_size, CHUNK)[:, r, :]
+
+    def compact_to_flat(self, per_rank: torch.Tensor) -> torch.Tensor:
+        """[world, shard_size] compact shards (rank-major) -> flat tensor in natural element order."""
+        return per_rank.view(self.world_size, self.num_blocks, CHUNK).permute(1, 0, 2).reshape(-1)
+
+    def bucket_ranges(self, bucket_elems: int) -> List[Tuple[int, int]]:
+        """Split [0, total) into contiguous buckets of ~bucket_elems whose bounds are multiples of
+        world_size * CHUNK, ordered from the END of the buffer (parameters registered last receive
+        their gradients first in backward)."""
+        gran = self.world_size * CHUNK
+        bucket_elems = max(_round_up(bucket_elems, gran), gran)
+        out = []
+        end = self.total
+        while end > 0:
+            start = max(0, end - bucket_elems)
+            out.append((start, end))
+            end = start
+        return out
+
+    def params_in_range(self, start: int, end: int) -> List[int]:
+        """Indices of the parameters that overlap [start, end)."""
+        return [i for i, (off, n) in enumerate(zip(self.offsets, self.numels)) if off < end and off + n > start]
+
+    def numel(self) -> int:
+        return sum(self.numels)

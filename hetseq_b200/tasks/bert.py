@@ -1,0 +1,172 @@
+"""BERT tasks (reference: tasks.py:186-285).
+
+``LanguageModelingTask`` (``--task bert``): BertForPreTraining on NVIDIA-format shards. Every file
+under ``--data`` whose name contains the split string is one shard (tasks.py:238-246);
+``--num_file`` truncates the list; ``--synthetic-data`` swaps in HDF5-shaped random batches
+(phase-1: 128 tokens / 20 predictions, phase-2: 512 / 80).
+
+``BertFineTuningTask`` (``--task bert_token_classification``): the reference's stub
+(tasks.py:261-285) references undefined names and cannot run; this is a working equivalent that
+trains ``BertForTokenClassification`` on ``.npz`` shards with ``input_ids, segment_ids,
+input_mask, labels``.
+"""
+from __future__ import annotations
+
+import os
+
+import numpy as np
+import torch
+
+from hetseq_b200.data.bert_dataset import BertH5pyData, ConBertH5pyData, SyntheticBertData
+from hetseq_b200.registry import register_task
+from hetseq_b200.tasks.base import Task
+
+
+@register_task('bert')
+class LanguageModelingTask(Task):
+    def __init__(self, args, dictionary=None):
+        super().__init__(args)
+        self.dictionary = dictionary
+
+    @staticmethod
+    def add_args(parser):
+        parser.add_argument('--data', type=str, help='path including data')
+        parser.add_argument('--dict', type=str, metavar='PATH of a file', help='PATH to dictionary')
+        parser.add_argument('--config_file', '--config-file', type=str, metavar='PATH of a file',
+                            help='PATH to bert model configuration', required=True)
+        parser.add_argument('--max_pred_length', '--max-pred-length', type=int, default=512,
+                            help='max number of tokens in a sentence')
+        parser.add_argument('--num_file', '--num-file', type=int, default=0,
+                            help='number of file to run, 0 for all')
+        parser.add_argument('--synthetic-data', action='store_true',
+                            help='train on HDF5-shaped random batches instead of --data')
+        parser.add_argument('--synthetic-seq-len', type=int, default=128)
+        parser.add_argument('--synthetic-max-predictions', type=int, default=20)
+        parser.add_argument('--synthetic-num-samples', type=int, default=8192)
+        parser.add_argument('--checkpoint-activations', action='store_true',
+                            help='recompute encoder activations in backward in chunks of ceil(sqrt(L)) layers '
+                                 '(the reference has the code but never enables it: bert_modeling.py:470-476)')
+        parser.add_argument('--mlm-all-positions', action='store_true',
+                            help='run the MLM decoder + loss over all B*S positions like the reference '
+                                 '(bert_modeling.py:878-882) instead of the labelled rows only')
+
+    @classmethod
+    def setup_task(cls, args, **kwargs):
+        dictionary = cls.load_dictionary(args.dict) if getattr(args, 'dict', None) else None
+        return cls(args, dictionary)
+
+    def build_model(self, args):
+        from hetseq_b200.models.bert import BertConfig, BertForPreTraining
+        config = BertConfig.from_json_file(args.config_file)
+        return BertForPreTraining(config, args=args)
+
+    def load_dataset(self, split, **kwargs):
+        args = self.args
+        if getattr(args, 'synthetic_data', False):
+            from hetseq_b200.models.bert import BertConfig
+            vocab = BertConfig.from_json_file(args.config_file).vocab_size
+            n = args.synthetic_num_samples if split == args.train_subset else max(64, args.synthetic_num_samples // 16)
+            ds = SyntheticBertData(n, args.synthetic_seq_len, args.synthetic_max_predictions, vocab,
+                                   seed=args.seed + (0 if split == args.train_subset else 1),
+                                   max_pred_length=args.max_pred_length)
+            self.datasets[split] = ConBertH5pyData([ds])
+            print('| synthetic {} sentences for split {}'.format(len(ds), split), flush=True)
+            return
+        path = args.data
+        if path is None or not os.path.exists(path):
+            raise FileNotFoundError('Dataset not found: ({})'.format(path))
+        files = [os.path.join(path, f) for f in os.listdir(path)] if os.path.isdir(path) else [path]
+        files = sorted([f for f in files if split in f])
+        if args.num_file > 0:
+            files = files[0:args.num_file]
+        assert len(files) > 0, 'no suitable file in split ***{}***'.format(split)
+        datasets = [BertH5pyData(f, max_pred_length=args.max_pred_length) for f in files]
+        dataset = ConBertH5pyData(datasets)
+        print('| loaded {} sentences from: {}'.format(len(dataset), path), flush=True)
+        self.datasets[split] = dataset
+        print('| loading finished')
+
+    def sample_stats(self, sample):
+        # real tokens = attended positions (input_mask is sample[2]); computed on the host copy
+        input_ids, mask = sample[0], sample[2]
+        ntokens = int(mask.sum()) if mask.device.type == 'cpu' else int(input_ids.numel())
+        return int(input_ids.shape[0]), ntokens
+
+    def prepare_sample(self, sample, device):
+        """int64 on disk, int32 on the wire: token ids and labels fit in 32 bits and the native
+        kernels consume int32 directly; PyTorch-path modules widen as needed."""
+        from hetseq_b200.utils import utils
+        if torch.device(device).type == 'cuda':
+            sample = [t.to(torch.int32) if t.dtype == torch.int64 else t for t in sample]
+        return utils.move_to_device(sample, device)
+
+
+@register_task('bert_token_classification')
+class BertFineTuningTask(Task):
+    def __init__(self, args, dictionary=None):
+        super().__init__(args)
+        self.dictionary = dictionary
+
+    @staticmethod
+    def add_args(parser):
+        parser.add_argument('--data', type=str, help='directory of .npz shards')
+        parser.add_argument('--dict', type=str, help='PATH to dictionary')
+        parser.add_argument('--config_file', '--config-file', type=str, required=True)
+        parser.add_argument('--num_label', '--num-label', type=int, default=3)
+
+    @classmethod
+    def setup_task(cls, args, **kwargs):
+        dictionary = cls.load_dictionary(args.dict) if getattr(args, 'dict', None) else None
+        return cls(args, dictionary)
+
+    def build_model(self, args):
+        from hetseq_b200.models.bert import BertConfig, BertForTokenClassification
+        config = BertConfig.from_json_file(args.config_file)
+        return _TokenClassificationLoss(BertForTokenClassification(config, args.num_label))
+
+    def load_dataset(self, split, **kwargs):
+        path = self.args.data
+        files = [os.path.join(path, f) for f in os.listdir(path)] if os.path.isdir(path) else [path]
+        files = sorted(f for f in files if split in f and f.endswith('.npz'))
+        assert len(files) > 0, 'no suitable file in split ***{}***'.format(split)
+        self.datasets[split] = _NpzTokenDataset(files)
+
+
+class _TokenClassificationLoss(torch.nn.Module):
+    """Adapts the head to the framework's ``model(*sample) -> loss`` contract."""
+
+    def __init__(self, head):
+        super().__init__()
+        self.head = head
+
+    def forward(self, input_ids, segment_ids, input_mask, labels):
+        return self.head(input_ids.long(), segment_ids.long(), input_mask.long(), labels.long())
+
+
+class _NpzTokenDataset(torch.utils.data.Dataset):
+    def __init__(self, files):
+        arrs = [np.load(f) for f in files]
+        self.a = {k: np.concatenate([z[k] for z in arrs]) for k in ('input_ids', 'segment_ids', 'input_mask', 'labels')}
+
+    def __len__(self):
+        return len(self.a['input_ids'])
+
+    def __getitem__(self, i):
+        return [torch.from_numpy(self.a[k][i].astype(np.int64)) for k in ('input_ids', 'segment_ids', 'input_mask', 'labels')]
+
+    def ordered_indices(self):
+        return np.arange(len(self))
+
+    def num_tokens(self, i):
+        return self.a['input_ids'].shape[1]
+
+    def sizes_array(self):
+        return np.full(len(self), self.a['input_ids'].shape[1], dtype=np.int64)
+
+    def collater(self, samples):
+        if len(samples) == 0:
+            return None
+        return [torch.stack([s[k] for s in samples]) for k in range(4)]
+
+    def set_epoch(self, epoch):
+        pass
