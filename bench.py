@@ -1,0 +1,368 @@
+#!/usr/bin/env python
+"""Headline benchmark: BERT pre-training throughput (sequences/s), seq 128, on N B200s of one node.
+
+    python bench.py --gpus 1 --steps 20 --warmup 5
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 \
+        --master-port 29500 bench.py --gpus 8 --steps 20 --warmup 5
+    python bench.py --impl reference ...      # the unmodified reference from baseline/_ref
+
+Config (BASELINE.json): BERT-large phase-1 (seq 128, 20 predictions), 32 sequences per GPU (global batch
+256 on 8 GPUs -> weak scaling), random-init weights, synthetic HDF5-shaped batches, fp16 with fp32
+master weights / Adam state and dynamic loss scaling; every step = forward + backward + gradient
+reduction + clip + Adam update, dropout on. Prints ONE JSON line on rank 0.
+
+Timing: W >= 3 untimed warm-up steps; exactly K timed steps bracketed by barrier + synchronize on both
+sides, CUDA events on the training stream, max over ranks. "value" feeds device-resident batches;
+"e2e" goes through the same public call (Controller.train_step) but every step copies its batch from
+pinned host memory and reads the loss back to the host. The per-step working set (fp16 weights +
+fp32 gradients + master/Adam state + activations, > 5 GB for BERT-large) is far larger than the 126 MB
+L2, so no explicit flush is needed between iterations; "config.l2" says so.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+MODELS = {
+    'bert-large': dict(hidden_size=1024, num_hidden_layers=24, num_attention_heads=16, intermediate_size=4096),
+    'bert-base': dict(hidden_size=768, num_hidden_layers=12, num_attention_heads=12, intermediate_size=3072),
+    'bert-tiny': dict(hidden_size=128, num_hidden_layers=2, num_attention_heads=2, intermediate_size=512),
+}
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=20)
+    ap.add_argument('--warmup', type=int, default=5)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--model', default='bert-large', choices=sorted(MODELS))
+    ap.add_argument('--batch', type=int, default=32, help='sequences per GPU per step')
+    ap.add_argument('--seq-len', type=int, default=128)
+    ap.add_argument('--max-predictions', type=int, default=None)
+    ap.add_argument('--dtype', default='fp16', choices=['fp16', 'bf16', 'fp32'])
+    ap.add_argument('--dp-backend', default='auto', choices=['auto', 'fused', 'nccl'])
+    ap.add_argument('--kernels', default='auto', choices=['auto', 'native', 'torch'])
+    ap.add_argument('--cuda-graph', action='store_true')
+    ap.add_argument('--no-e2e', action='store_true')
+    return ap.parse_args()
+
+
+def write_config(model_name, tmpdir):
+    cfg = dict(vocab_size=30522, hidden_act='gelu', hidden_dropout_prob=0.1, attention_probs_dropout_prob=0.1,
+               max_position_embeddings=512, type_vocab_size=2, initializer_range=0.02)
+    cfg.update(MODELS[model_name])
+    path = os.path.join(tmpdir, 'bert_config.json')
+    with open(path, 'w') as f:
+        json.dump(cfg, f)
+    vocab = os.path.join(tmpdir, 'vocab.txt')
+    with open(vocab, 'w') as f:
+        f.write('\n'.join('tok%d' % i for i in range(64)))
+    return path, vocab
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons with nvidia-smi while the timed region runs."""
+
+    FIELDS = ('clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,'
+              'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,'
+              'clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index=0):
+        super().__init__(daemon=True)
+        self.index = index
+        self.samples = []
+        self._stop = threading.Event()
+
+    def run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.FIELDS,
+                                      '--format=csv,noheader,nounits'], capture_output=True, text=True, timeout=5).stdout
+                parts = [p.strip() for p in out.strip().split(',')]
+                if len(parts) >= 7:
+                    self.samples.append(parts)
+            except Exception:
+                pass
+            self._stop.wait(0.2)
+
+    def stop(self):
+        self._stop.set()
+        self.join(timeout=6)
+
+    def summary(self):
+        if not self.samples:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['unsampled']}
+        sm = [float(s[0]) for s in self.samples if s[0].replace('.', '').isdigit()]
+        mx = [float(s[1]) for s in self.samples if s[1].replace('.', '').isdigit()]
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        reasons = [n for k, n in enumerate(names) if any(s[3 + k].lower().startswith('active') for s in self.samples)]
+        return {'sm_mhz': statistics.median(sm) if sm else None, 'sm_max_mhz': max(mx) if mx else None,
+                'reasons': reasons, 'samples': len(self.samples)}
+
+
+def dist_env(a):
+    rank = int(os.environ.get('RANK', 0))
+    world = int(os.environ.get('WORLD_SIZE', 1))
+    local = int(os.environ.get('LOCAL_RANK', 0))
+    if world != a.gpus and world > 1:
+        a.gpus = world
+    return rank, world, local
+
+
+def max_over_ranks(ms, world, device):
+    import torch
+    import torch.distributed as dist
+    if world <= 1:
+        return ms
+    t = torch.tensor([ms], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def barrier_sync(world):
+    import torch
+    import torch.distributed as dist
+    if world > 1:
+        dist.barrier(device_ids=[torch.cuda.current_device()])
+    torch.cuda.synchronize()
+
+
+def make_batches(a, n, vocab, seed):
+    """n collated host batches (list of five int64 tensors), pinned."""
+    from hetseq_b200.data.bert_dataset import SyntheticBertData
+    maxp = a.max_predictions or (20 if a.seq_len <= 128 else 80)
+    ds = SyntheticBertData(n * a.batch, a.seq_len, maxp, vocab, seed=seed)
+    out = []
+    for i in range(n):
+        b = ds.fetch_rows(list(range(i * a.batch, (i + 1) * a.batch)))
+        out.append([t.pin_memory() for t in b])
+    return out
+
+
+def timed_loop(step_fn, batches, warmup, steps, world, device):
+    import torch
+    for i in range(warmup):
+        step_fn(batches[i % len(batches)])
+    barrier_sync(world)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        step_fn(batches[(warmup + i) % len(batches)])
+    e1.record()
+    barrier_sync(world)
+    return max_over_ranks(e0.elapsed_time(e1), world, device)
+
+
+# --------------------------------------------------------------------------------------------------
+def run_ours(a):
+    import torch
+    rank, world, local = dist_env(a)
+    torch.cuda.set_device(local)
+    device = torch.device('cuda', local)
+    tmp = tempfile.mkdtemp(prefix='hsbench')
+    cfg_path, vocab_path = write_config(a.model, tmp)
+
+    from hetseq_b200 import options, registry
+    from hetseq_b200.controller import Controller
+    from hetseq_b200.ops import lib
+    from hetseq_b200.parallel import distributed_utils
+
+    argv = ['--config_file', cfg_path, '--max-sentences', str(a.batch), '--synthetic-data',
+            '--synthetic-seq-len', str(a.seq_len), '--lr', '1e-4', '--warmup-updates', '100',
+            '--total-num-update', '100000', '--weight-decay', '0.01', '--clip-norm', '1.0',
+            '--adam-betas', '(0.9, 0.999)', '--no-save', '--log-format', 'none', '--fast-stat-sync',
+            '--distributed-world-size', str(world), '--distributed-rank', str(rank), '--device-id', str(local),
+            '--dp-backend', a.dp_backend, '--kernels', a.kernels, '--save-dir', tmp]
+    if a.dtype == 'fp16':
+        argv.append('--fp16')
+    elif a.dtype == 'bf16':
+        argv.append('--bf16')
+    if a.cuda_graph:
+        argv.append('--cuda-graph')
+    args = options.make_args('bert', 'adam', 'PolynomialDecayScheduler', argv)
+    if world > 1:
+        args.distributed_init_method = 'env://'
+        distributed_utils.distributed_init(args)
+    torch.manual_seed(args.seed)
+    task = registry.lookup('task', 'bert').setup_task(args)
+    model = task.build_model(args)
+    controller = Controller(args, task, model)
+    controller.optimizer  # build engine
+
+    nb = 8
+    host = make_batches(a, nb, model.config.vocab_size, seed=1234 + rank)
+    dev = [task.prepare_sample(b, device) for b in host]
+    h2d_bytes = sum(t.to(torch.int32).numel() * 4 if t.dtype == torch.int64 else t.numel() * t.element_size()
+                    for t in host[0])
+
+    def step_device(batch):
+        # device-resident batch: _prepare_sample's copy is a no-op
+        controller.train_step([batch])
+
+    def step_e2e(batch):
+        out = controller.train_step([batch])     # pinned host -> device copy inside; loss read back to host
+        return out
+
+    sampler = ClockSampler(local) if rank == 0 else None
+    launches0 = lib.launch_count() if lib.available() else 0
+    if sampler:
+        sampler.start()
+    ms = timed_loop(step_device, dev, a.warmup, a.steps, world, device)
+    if sampler:
+        sampler.stop()
+    launches = (lib.launch_count() - launches0) if lib.available() else 0
+    # launches counted over warm-up + timed steps; report the timed share
+    launches_timed = int(round(launches * a.steps / max(1, a.steps + a.warmup)))
+
+    e2e = None
+    if not a.no_e2e:
+        ms_e2e = timed_loop(step_e2e, host, 3, a.steps, world, device)
+        e2e = {'value': round(world * a.batch * a.steps / (ms_e2e / 1e3), 2), 'unit': 'sequences/s',
+               'ms_per_step': round(ms_e2e / a.steps, 3), 'h2d_bytes_per_step': int(h2d_bytes),
+               'd2h_bytes_per_step': 7 * 8}
+
+    if rank == 0:
+        value = world * a.batch * a.steps / (ms / 1e3)
+        baseline = published_baseline(world)
+        out = {
+            'metric': 'BERT seq%d sequences/sec' % a.seq_len, 'value': round(value, 2), 'unit': 'sequences/s',
+            'n_gpus': world, 'steps': a.steps, 'warmup': a.warmup, 'ms_per_step': round(ms / a.steps, 3),
+            'higher_is_better': True, 'scaling': 'weak',
+            'vs_baseline': round(value / baseline, 3) if baseline else None,
+            'dtype': a.dtype, 'data': 'synthetic (HDF5 phase-%d shaped batches, random-init weights)' % (1 if a.seq_len <= 128 else 2),
+            'impl': 'ours',
+            'config': {'model': a.model, 'global_batch': world * a.batch, 'per_gpu_batch': a.batch, 'seq_len': a.seq_len,
+                       'parallelism': 'dp%d' % world, 'dp_backend': controller.dp.name, 'optimizer': 'adam',
+                       'kernels': 'native sm_100a' if controller._model.native is not None else 'torch',
+                       'l2': 'per-step working set (weights+grads+Adam state+activations) >> 126 MB L2; no flush needed',
+                       'cuda_graph': bool(a.cuda_graph)},
+            'clocks': sampler.summary() if sampler else None,
+            'gpu_launches': launches_timed,
+        }
+        if e2e:
+            out['e2e'] = e2e
+        print(json.dumps(out), flush=True)
+    controller.close()
+    if world > 1:
+        torch.distributed.destroy_process_group()
+
+
+def published_baseline(world):
+    """seq/s derived from the reference README's table (batch / s-per-step); only 4..32 GPUs exist,
+    hardware unspecified. For other GPU counts there is no published number."""
+    table = {4: 49.2, 8: 95.2, 16: 183.3, 32: 327.6}
+    return table.get(world)
+
+
+# --------------------------------------------------------------------------------------------------
+def run_reference(a):
+    """The unmodified reference (baseline/_ref): its options parser, LanguageModelingTask, BertForPreTraining,
+    Controller.train_step (DDP + its Adam). fp32 -- the reference has no fp16 path (options.py:11)."""
+    ref = os.path.join(ROOT, 'baseline', '_ref')
+    if not os.path.exists(os.path.join(ref, 'controller.py')):
+        print(json.dumps({'impl': 'reference', 'unavailable': 'baseline/_ref not installed (run baseline/install_reference.sh)'}))
+        return
+    try:
+        import types
+        import torch
+        # import-time dependencies of the reference that are not in this image and are never exercised here
+        for name in ('boto3', 'botocore', 'botocore.exceptions', 'h5py'):
+            if name not in sys.modules:
+                try:
+                    __import__(name)
+                except Exception:
+                    m = types.ModuleType(name)
+                    if name == 'botocore.exceptions':
+                        m.ClientError = type('ClientError', (Exception,), {})
+                    sys.modules[name] = m
+        sys.path.insert(0, ref)
+        rank, world, local = dist_env(a)
+        torch.cuda.set_device(local)
+        device = torch.device('cuda', local)
+        tmp = tempfile.mkdtemp(prefix='hsref')
+        cfg_path, vocab_path = write_config(a.model, tmp)
+
+        import options as ref_options        # noqa: E402  (reference modules, flat imports)
+        import tasks as ref_tasks            # noqa: E402
+        import distributed_utils as ref_dist  # noqa: E402
+        from controller import Controller as RefController  # noqa: E402
+
+        parser = ref_options.get_training_parser(task='bert', optimizer='adam', lr_scheduler='PolynomialDecayScheduler')
+        argv = ['--task', 'bert', '--data', tmp, '--dict', vocab_path, '--config_file', cfg_path,
+                '--max-sentences', str(a.batch), '--lr', '1e-4', '--warmup-updates', '100',
+                '--total-num-update', '100000', '--weight-decay', '0.01', '--clip-norm', '1.0',
+                '--adam-betas', '(0.9, 0.999)', '--no-save', '--fast-stat-sync', '--save-dir', tmp,
+                '--distributed-world-size', str(world), '--distributed-rank', str(rank), '--device-id', str(local)]
+        args = ref_options.parse_args_and_arch(parser, argv)
+        if world > 1:
+            args.distributed_init_method = 'env://'
+            ref_dist.distributed_init(args)
+        torch.manual_seed(args.seed)
+        task = ref_tasks.LanguageModelingTask.setup_task(args)
+        model = task.build_model(args)
+        controller = RefController(args, task, model)
+
+        nb = 8
+        host = make_batches(a, nb, model.config.vocab_size, seed=1234 + rank)
+        dev = [[t.cuda(non_blocking=True) for t in b] for b in host]
+        h2d_bytes = sum(t.numel() * t.element_size() for t in host[0])
+
+        def step(batch):
+            controller.train_step([batch])
+
+        sampler = ClockSampler(local) if rank == 0 else None
+        if sampler:
+            sampler.start()
+        ms = timed_loop(step, dev, a.warmup, a.steps, world, device)
+        if sampler:
+            sampler.stop()
+        e2e = None
+        if not a.no_e2e:
+            ms_e2e = timed_loop(step, host, 2, a.steps, world, device)
+            e2e = {'value': round(world * a.batch * a.steps / (ms_e2e / 1e3), 2), 'unit': 'sequences/s',
+                   'ms_per_step': round(ms_e2e / a.steps, 3), 'h2d_bytes_per_step': int(h2d_bytes),
+                   'd2h_bytes_per_step': 6 * 8}
+        if rank == 0:
+            value = world * a.batch * a.steps / (ms / 1e3)
+            baseline = published_baseline(world)
+            out = {'metric': 'BERT seq%d sequences/sec' % a.seq_len, 'value': round(value, 2), 'unit': 'sequences/s',
+                   'n_gpus': world, 'steps': a.steps, 'warmup': a.warmup, 'ms_per_step': round(ms / a.steps, 3),
+                   'higher_is_better': True, 'scaling': 'weak',
+                   'vs_baseline': round(value / baseline, 3) if baseline else None, 'dtype': 'fp32',
+                   'data': 'synthetic (HDF5 phase-1 shaped batches, random-init weights)', 'impl': 'reference',
+                   'config': {'model': a.model, 'global_batch': world * a.batch, 'per_gpu_batch': a.batch,
+                              'seq_len': a.seq_len, 'parallelism': 'dp%d' % world, 'dp_backend': 'torch DDP + NCCL',
+                              'note': 'unmodified reference; it has no fp16 path, runs fp32',
+                              'l2': 'per-step working set >> 126 MB L2; no flush needed'},
+                   'clocks': sampler.summary() if sampler else None, 'gpu_launches': 0}
+            if e2e:
+                out['e2e'] = e2e
+            # the reference silences print on non-master ranks only; rank 0 prints normally
+            print(json.dumps(out), flush=True)
+        if world > 1:
+            torch.distributed.destroy_process_group()
+    except Exception as e:  # the contract: report unavailability in one line, exit 0
+        import traceback
+        traceback.print_exc(file=sys.stderr)
+        if int(os.environ.get('RANK', 0)) == 0:
+            print(json.dumps({'impl': 'reference', 'unavailable': '%s: %s' % (type(e).__name__, str(e)[:200])}))
+
+
+if __name__ == '__main__':
+    a = parse()
+    if a.impl == 'reference':
+        run_reference(a)
+    else:
+        run_ours(a)

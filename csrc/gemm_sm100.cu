@@ -43,6 +43,7 @@ struct GemmParams {
   uint32_t b_lbo, b_sbo, b_kadv;
   int act, accumulate;
   float alpha;
+  const float* alpha_dev;
   int vec_ok;  // C/aux rows are 16-byte aligned -> vector loads/stores allowed
 };
 
@@ -225,6 +226,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const InT* bias = reinterpret_cast<const InT*>(p.bias);
     OutT* C = reinterpret_cast<OutT*>(p.C);
     const bool vec = p.vec_ok != 0;
+    const float alpha = p.alpha * (p.alpha_dev != nullptr ? *p.alpha_dev : 1.0f);
     int as = 0;
     uint32_t aphase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -250,7 +252,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         tmem_ld_wait();
         float v[32];
 #pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]) * p.alpha;
+        for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]) * alpha;
         if (bias != nullptr) {
 #pragma unroll
           for (int i = 0; i < 32; ++i) v[i] += sb[c * 32 + i];
@@ -371,7 +373,7 @@ static int launch_gemm(const hs_gemm_args& a, cudaStream_t stream) {
   // 1024 B apart; a k-step of 16 rows is 2048 B.
   p.a_lbo = a.a_mn_major ? BK * 128 : 16; p.a_sbo = 1024; p.a_kadv = a.a_mn_major ? 2048 : 32;
   p.b_lbo = a.b_mn_major ? BK * 128 : 16; p.b_sbo = 1024; p.b_kadv = a.b_mn_major ? 2048 : 32;
-  p.act = a.act; p.accumulate = a.accumulate; p.alpha = a.alpha;
+  p.act = a.act; p.accumulate = a.accumulate; p.alpha = a.alpha; p.alpha_dev = a.alpha_dev;
   const size_t osz = sizeof(OutT);
   bool vec = (reinterpret_cast<uintptr_t>(a.C) % 16 == 0) && ((a.ldc * osz) % 16 == 0);
   if (a.aux_out) vec = vec && (reinterpret_cast<uintptr_t>(a.aux_out) % 16 == 0) && ((a.ldaux * 2) % 16 == 0);

@@ -1,0 +1,374 @@
+// hetseq_b200 -- fused (bias +) dropout + residual + LayerNorm, forward and backward.
+//
+//   z = residual + dropout(x + bias)          y = gamma * (z - mean) / sqrt(var + eps) + beta
+//
+// TF-style LayerNorm of the reference: biased variance, eps = 1e-12 *inside* the sqrt
+// (bert_modeling.py:277-289). Replaces, per call, the GEMM-output dropout kernel, the residual add and
+// the ~9 elementwise/reduction launches of BertLayerNorm in BertSelfOutput / BertOutput
+// (bert_modeling.py:387-391, 423-427) and the plain LayerNorm of the MLM
+// transform and the embeddings (bert_modeling.py:313-319, 525-528).
+//
+// One warp owns one row: the row lives in registers (H <= 2048), statistics are two shuffles-only
+// passes over registers (mean, then centred sum of squares), every global access is a 128-bit vector.
+// Dropout masks come from Philox keyed by (step seed, site, element) -- backward recomputes them, so
+// no mask tensor exists. The kernels are HBM-bound: forward moves 2 reads + 2 writes of [M,H] 16-bit.
+#include "common.cuh"
+#include "host.h"
+#include "../include/hetseq_b200.h"
+
+namespace hs {
+
+constexpr int LN_MAXV = 8;             // vectors (8 elements each) per lane -> H <= 2048
+constexpr int LN_ROWS_PER_BLOCK = 4;   // one warp per row
+constexpr int LN_THREADS = LN_ROWS_PER_BLOCK * 32;
+
+template <typename T>
+__device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
+  float2 a = Cvt<T>::unpack2(u.x), b = Cvt<T>::unpack2(u.y), c = Cvt<T>::unpack2(u.z), d = Cvt<T>::unpack2(u.w);
+  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+}
+template <typename T>
+__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
+  uint4 u;
+  u.x = Cvt<T>::pack2(f[0], f[1]); u.y = Cvt<T>::pack2(f[2], f[3]);
+  u.z = Cvt<T>::pack2(f[4], f[5]); u.w = Cvt<T>::pack2(f[6], f[7]);
+  return u;
+}
+
+// keep/scale factors for the 8 consecutive elements starting at flat element index e0 (e0 % 8 == 0)
+__device__ __forceinline__ void dropout_mask8(const long long* seed_ptr, uint32_t site, uint64_t e0, float p,
+                                              float scale, float (&mk)[8]) {
+  const uint64_t seed = static_cast<uint64_t>(seed_ptr[0]) * 0x9E3779B97F4A7C15ull + static_cast<uint64_t>(seed_ptr[1]);
+  const float4 r0 = philox_uniform4(seed, site, e0 >> 2);
+  const float4 r1 = philox_uniform4(seed, site, (e0 >> 2) + 1);
+  mk[0] = r0.x >= p ? scale : 0.f; mk[1] = r0.y >= p ? scale : 0.f;
+  mk[2] = r0.z >= p ? scale : 0.f; mk[3] = r0.w >= p ? scale : 0.f;
+  mk[4] = r1.x >= p ? scale : 0.f; mk[5] = r1.y >= p ? scale : 0.f;
+  mk[6] = r1.z >= p ? scale : 0.f; mk[7] = r1.w >= p ? scale : 0.f;
+}
+
+struct LnFwdParams {
+  const void* x; const void* bias; const void* residual; const void* gamma; const void* beta;
+  void* y; void* z; float* mean; float* rstd;
+  int M, H; float eps; float p; const long long* seed; uint32_t site;
+  int post_dropout;  // 1: y = dropout(LN(z)) (embeddings) instead of z = res + dropout(x)
+};
+
+template <typename T, int NV>
+__global__ void __launch_bounds__(LN_THREADS) ln_fwd_kernel(LnFwdParams P) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * LN_ROWS_PER_BLOCK + warp;
+  if (row >= P.M) return;
+  const int nvec = P.H >> 3;
+  const T* x = reinterpret_cast<const T*>(P.x) + static_cast<size_t>(row) * P.H;
+  const T* res = P.residual ? reinterpret_cast<const T*>(P.residual) + static_cast<size_t>(row) * P.H : nullptr;
+  const bool drop = P.p > 0.f;
+  const float scale = drop ? 1.f / (1.f - P.p) : 1.f;
+  float v[NV][8];
+  float sum = 0.f;
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {
+    const int vi = j * 32 + lane;
+    if (vi < nvec) {
+      float f[8];
+      unpack8<T>(reinterpret_cast<const uint4*>(x)[vi], f);
+      if (P.bias) {
+        float b[8];
+        unpack8<T>(reinterpret_cast<const uint4*>(P.bias)[vi], b);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) f[k] += b[k];
+      }
+      if (drop && !P.post_dropout) {
+        float mk[8];
+        dropout_mask8(P.seed, P.site, static_cast<uint64_t>(row) * P.H + vi * 8, P.p, scale, mk);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) f[k] *= mk[k];
+      }
+      if (res) {
+        float r[8];
+        unpack8<T>(reinterpret_cast<const uint4*>(res)[vi], r);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) f[k] += r[k];
+      }
+      if (P.z) reinterpret_cast<uint4*>(reinterpret_cast<T*>(P.z) + static_cast<size_t>(row) * P.H)[vi] = pack8<T>(f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) { v[j][k] = f[k]; sum += f[k]; }
+    }
+  }
+  const float mean = warp_sum(sum) / P.H;
+  float sq = 0.f;
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {
+    if (j * 32 + lane < nvec) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) { const float d = v[j][k] - mean; sq += d * d; }
+    }
+  }
+  const float rstd = rsqrtf(warp_sum(sq) / P.H + P.eps);
+  if (lane == 0) {
+    if (P.mean) P.mean[row] = mean;
+    if (P.rstd) P.rstd[row] = rstd;
+  }
+  T* y = reinterpret_cast<T*>(P.y) + static_cast<size_t>(row) * P.H;
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {
+    const int vi = j * 32 + lane;
+    if (vi < nvec) {
+      float g[8], b[8], o[8];
+      unpack8<T>(reinterpret_cast<const uint4*>(P.gamma)[vi], g);
+      unpack8<T>(reinterpret_cast<const uint4*>(P.beta)[vi], b);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) o[k] = g[k] * ((v[j][k] - mean) * rstd) + b[k];
+      if (drop && P.post_dropout) {
+        float mk[8];
+        dropout_mask8(P.seed, P.site, static_cast<uint64_t>(row) * P.H + vi * 8, P.p, scale, mk);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) o[k] *= mk[k];
+      }
+      reinterpret_cast<uint4*>(y)[vi] = pack8<T>(o);
+    }
+  }
+}
+
+struct LnBwdParams {
+  const void* dy; const void* z; const void* gamma; const float* mean; const float* rstd;
+  void* dz;       // gradient w.r.t. z (the residual path), 16-bit
+  void* dx;       // gradient w.r.t. x = dz * dropout mask (NULL when p == 0 and dz suffices)
+  float* part_dgamma; float* part_dbeta;   // [gridDim.x, H] partial sums (scratch)
+  int M, H; float p; const long long* seed; uint32_t site;
+  int post_dropout;  // 1: dy is first multiplied by the mask (embeddings: y = dropout(LN(z)))
+  int rows_per_block;
+};
+
+template <typename T, int NV>
+__global__ void __launch_bounds__(LN_THREADS) ln_bwd_kernel(LnBwdParams P) {
+  extern __shared__ float sm[];  // [LN_ROWS_PER_BLOCK][2][H] warp-private partials
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nvec = P.H >> 3;
+  const bool drop = P.p > 0.f;
+  const float scale = drop ? 1.f / (1.f - P.p) : 1.f;
+  float dg[NV][8], db[NV][8];
+#pragma unroll
+  for (int j = 0; j < NV; ++j)
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { dg[j][k] = 0.f; db[j][k] = 0.f; }
+
+  const int row0 = blockIdx.x * P.rows_per_block;
+  const int row_end = min(P.M, row0 + P.rows_per_block);
+  for (int row = row0 + warp; row < row_end; row += LN_ROWS_PER_BLOCK) {
+    const T* dy = reinterpret_cast<const T*>(P.dy) + static_cast<size_t>(row) * P.H;
+    const T* z = reinterpret_cast<const T*>(P.z) + static_cast<size_t>(row) * P.H;
+    const float mean = P.mean[row], rstd = P.rstd[row];
+    float xh[NV][8], gy[NV][8];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int vi = j * 32 + lane;
+      if (vi < nvec) {
+        float d[8], zz[8], g[8];
+        unpack8<T>(reinterpret_cast<const uint4*>(dy)[vi], d);
+        unpack8<T>(reinterpret_cast<const uint4*>(z)[vi], zz);
+        unpack8<T>(reinterpret_cast<const uint4*>(P.gamma)[vi], g);
+        if (drop && P.post_dropout) {
+          float mk[8];
+          dropout_mask8(P.seed, P.site, static_cast<uint64_t>(row) * P.H + vi * 8, P.p, scale, mk);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) d[k] *= mk[k];
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const float h = (zz[k] - mean) * rstd;
+          xh[j][k] = h;
+          dg[j][k] += d[k] * h;
+          db[j][k] += d[k];
+          const float t = d[k] * g[k];
+          gy[j][k] = t;
+          s1 += t;
+          s2 += t * h;
+        }
+      }
+    }
+    s1 = warp_sum(s1) / P.H;
+    s2 = warp_sum(s2) / P.H;
+    T* dz = reinterpret_cast<T*>(P.dz) + static_cast<size_t>(row) * P.H;
+    T* dx = P.dx ? reinterpret_cast<T*>(P.dx) + static_cast<size_t>(row) * P.H : nullptr;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int vi = j * 32 + lane;
+      if (vi < nvec) {
+        float o[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) o[k] = rstd * (gy[j][k] - s1 - xh[j][k] * s2);
+        reinterpret_cast<uint4*>(dz)[vi] = pack8<T>(o);
+        if (dx) {
+          if (drop && !P.post_dropout) {
+            float mk[8];
+            dropout_mask8(P.seed, P.site, static_cast<uint64_t>(row) * P.H + vi * 8, P.p, scale, mk);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) o[k] *= mk[k];
+          }
+          reinterpret_cast<uint4*>(dx)[vi] = pack8<T>(o);
+        }
+      }
+    }
+  }
+  // combine the 4 warps' gamma/beta partials through shared memory, one partial row per block
+  float* sg = sm + static_cast<size_t>(warp) * 2 * P.H;
+  float* sb = sg + P.H;
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {
+    const int vi = j * 32 + lane;
+    if (vi < nvec) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) { sg[vi * 8 + k] = dg[j][k]; sb[vi * 8 + k] = db[j][k]; }
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < P.H; i += blockDim.x) {
+    float a = 0.f, b = 0.f;
+#pragma unroll
+    for (int w = 0; w < LN_ROWS_PER_BLOCK; ++w) {
+      a += sm[static_cast<size_t>(w) * 2 * P.H + i];
+      b += sm[static_cast<size_t>(w) * 2 * P.H + P.H + i];
+    }
+    P.part_dgamma[static_cast<size_t>(blockIdx.x) * P.H + i] = a;
+    P.part_dbeta[static_cast<size_t>(blockIdx.x) * P.H + i] = b;
+  }
+}
+
+// out[h] (= or +=) sum over parts of part[part, h]; fp32 output (the flat main-grad buffer)
+__global__ void __launch_bounds__(256)
+colsum_parts_kernel(const float* __restrict__ part, int nparts, int H, float* __restrict__ out, int accumulate) {
+  const int h = blockIdx.x * blockDim.x + threadIdx.x;
+  if (h >= H) return;
+  float a = 0.f;
+  for (int i = 0; i < nparts; ++i) a += part[static_cast<size_t>(i) * H + h];
+  out[h] = accumulate ? out[h] + a : a;
+}
+
+// Column sums of a 16-bit [M, N] matrix (bias gradients): stage 1 partials over row slabs.
+template <typename T>
+__global__ void __launch_bounds__(256)
+colsum_partial_kernel(const T* __restrict__ x, int M, int N, int ld, int rows_per_block, float* __restrict__ part) {
+  // each thread owns 8 consecutive columns
+  const int c8 = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c8 * 8 >= N) return;
+  const int r0 = blockIdx.y * rows_per_block, r1 = min(M, r0 + rows_per_block);
+  float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  for (int r = r0; r < r1; ++r) {
+    float f[8];
+    unpack8<T>(*reinterpret_cast<const uint4*>(x + static_cast<size_t>(r) * ld + c8 * 8), f);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc[k] += f[k];
+  }
+  float* dst = part + static_cast<size_t>(blockIdx.y) * N + c8 * 8;
+#pragma unroll
+  for (int k = 0; k < 8; ++k)
+    if (c8 * 8 + k < N) dst[k] = acc[k];
+}
+
+static int ln_check(const char* who, int M, int H) {
+  if (M <= 0 || H <= 0 || H % 8 != 0 || H > LN_MAXV * 256) {
+    set_last_error("%s: unsupported shape M=%d H=%d (H must be a multiple of 8, <= %d)", who, M, H, LN_MAXV * 256);
+    return 1;
+  }
+  return 0;
+}
+
+}  // namespace hs
+
+using namespace hs;
+
+extern "C" int hs_ln_fwd(const void* x, const void* bias, const void* residual, const void* gamma, const void* beta,
+                         void* y, void* z, float* mean, float* rstd, int M, int H, float eps, float dropout_p,
+                         const long long* seed, unsigned site, int post_dropout, int dtype, hs_stream_t stream) {
+  if (ln_check("hs_ln_fwd", M, H)) return 1;
+  if (dropout_p > 0.f && seed == nullptr) { set_last_error("hs_ln_fwd: dropout needs a seed pointer"); return 1; }
+  LnFwdParams P{x, bias, residual, gamma, beta, y, z, mean, rstd, M, H, eps, dropout_p, seed, site, post_dropout};
+  const int grid = (M + LN_ROWS_PER_BLOCK - 1) / LN_ROWS_PER_BLOCK;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int nv = (H + 255) / 256;
+#define HS_LN_FWD(T)                                                                 \
+  do {                                                                               \
+    if (nv <= 1) ln_fwd_kernel<T, 1><<<grid, LN_THREADS, 0, s>>>(P);                 \
+    else if (nv <= 2) ln_fwd_kernel<T, 2><<<grid, LN_THREADS, 0, s>>>(P);            \
+    else if (nv <= 4) ln_fwd_kernel<T, 4><<<grid, LN_THREADS, 0, s>>>(P);            \
+    else ln_fwd_kernel<T, 8><<<grid, LN_THREADS, 0, s>>>(P);                         \
+  } while (0)
+  if (dtype == HS_F16) HS_LN_FWD(__half);
+  else if (dtype == HS_BF16) HS_LN_FWD(__nv_bfloat16);
+  else { set_last_error("hs_ln_fwd: dtype must be f16 or bf16"); return 1; }
+#undef HS_LN_FWD
+  return post_launch("ln_fwd_kernel");
+}
+
+extern "C" int hs_ln_bwd_scratch_elems(int M, int H) {
+  const int blocks = num_sms() * 4;
+  const int rpb = (M + blocks - 1) / blocks;
+  const int rows_per_block = ((rpb + LN_ROWS_PER_BLOCK - 1) / LN_ROWS_PER_BLOCK) * LN_ROWS_PER_BLOCK;
+  const int grid = (M + rows_per_block - 1) / rows_per_block;
+  return 2 * grid * H;
+}
+
+extern "C" int hs_ln_bwd(const void* dy, const void* z, const void* gamma, const float* mean, const float* rstd,
+                         void* dz, void* dx, float* dgamma, float* dbeta, int accumulate_params, float* scratch,
+                         int M, int H, float dropout_p, const long long* seed, unsigned site, int post_dropout,
+                         int dtype, hs_stream_t stream) {
+  if (ln_check("hs_ln_bwd", M, H)) return 1;
+  if (scratch == nullptr) { set_last_error("hs_ln_bwd: scratch is required"); return 1; }
+  const int blocks = num_sms() * 4;
+  const int rpb = (M + blocks - 1) / blocks;
+  const int rows_per_block = ((rpb + LN_ROWS_PER_BLOCK - 1) / LN_ROWS_PER_BLOCK) * LN_ROWS_PER_BLOCK;
+  const int grid = (M + rows_per_block - 1) / rows_per_block;
+  float* part_g = scratch;
+  float* part_b = scratch + static_cast<size_t>(grid) * H;
+  LnBwdParams P{dy, z, gamma, mean, rstd, dz, dx, part_g, part_b, M, H, dropout_p, seed, site, post_dropout, rows_per_block};
+  const size_t smem = static_cast<size_t>(LN_ROWS_PER_BLOCK) * 2 * H * sizeof(float);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (smem > 48 * 1024) { set_last_error("hs_ln_bwd: H=%d needs %zu B of shared memory", H, smem); return 1; }
+  const int nv = (H + 255) / 256;
+#define HS_LN_BWD(T)                                                                    \
+  do {                                                                                  \
+    if (nv <= 1) ln_bwd_kernel<T, 1><<<grid, LN_THREADS, smem, s>>>(P);                 \
+    else if (nv <= 2) ln_bwd_kernel<T, 2><<<grid, LN_THREADS, smem, s>>>(P);            \
+    else if (nv <= 4) ln_bwd_kernel<T, 4><<<grid, LN_THREADS, smem, s>>>(P);            \
+    else ln_bwd_kernel<T, 8><<<grid, LN_THREADS, smem, s>>>(P);                         \
+  } while (0)
+  if (dtype == HS_F16) HS_LN_BWD(__half);
+  else if (dtype == HS_BF16) HS_LN_BWD(__nv_bfloat16);
+  else { set_last_error("hs_ln_bwd: dtype must be f16 or bf16"); return 1; }
+#undef HS_LN_BWD
+  if (post_launch("ln_bwd_kernel")) return 1;
+  if (dgamma) {
+    colsum_parts_kernel<<<(H + 255) / 256, 256, 0, s>>>(part_g, grid, H, dgamma, accumulate_params);
+    if (post_launch("colsum_parts_kernel")) return 1;
+  }
+  if (dbeta) {
+    colsum_parts_kernel<<<(H + 255) / 256, 256, 0, s>>>(part_b, grid, H, dbeta, accumulate_params);
+    if (post_launch("colsum_parts_kernel")) return 1;
+  }
+  return 0;
+}
+
+extern "C" int hs_colsum_scratch_elems(int M, int N) {
+  const int slabs = (M + 63) / 64 < 64 ? (M + 63) / 64 : 64;
+  return slabs * N;
+}
+
+extern "C" int hs_colsum(const void* x, int M, int N, int ld, float* out, int accumulate, float* scratch, int dtype,
+                         hs_stream_t stream) {
+  if (M <= 0 || N <= 0 || ld % 8 != 0 || scratch == nullptr) {
+    set_last_error("hs_colsum: bad arguments M=%d N=%d ld=%d scratch=%p", M, N, ld, (void*)scratch);
+    return 1;
+  }
+  const int slabs = (M + 63) / 64 < 64 ? (M + 63) / 64 : 64;
+  const int rows_per_block = (M + slabs - 1) / slabs;
+  dim3 grid(((N + 7) / 8 + 255) / 256, slabs);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (dtype == HS_F16) colsum_partial_kernel<__half><<<grid, 256, 0, s>>>((const __half*)x, M, N, ld, rows_per_block, scratch);
+  else if (dtype == HS_BF16) colsum_partial_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>((const __nv_bfloat16*)x, M, N, ld, rows_per_block, scratch);
+  else { set_last_error("hs_colsum: dtype must be f16 or bf16"); return 1; }
+  if (post_launch("colsum_partial_kernel")) return 1;
+  colsum_parts_kernel<<<(N + 255) / 256, 256, 0, s>>>(scratch, slabs, N, out, accumulate);
+  return post_launch("colsum_parts_kernel");
+}

@@ -90,7 +90,7 @@ static int run_case(const Case& c) {
   g.a_mn_major = c.a_mn; g.b_mn_major = c.b_mn; g.in_dtype = c.bf ? HS_BF16 : HS_F16;
   g.out_dtype = c.out_f32 ? HS_F32 : g.in_dtype; g.bias = c.bias ? dbias : nullptr; g.act = c.act;
   g.aux_out = (c.act == HS_ACT_GELU) ? daux_out : nullptr; g.aux_in = (c.act == HS_ACT_DGELU_MUL) ? daux_in : nullptr;
-  g.ldaux = ldaux; g.accumulate = c.accumulate; g.alpha = 1.0f;
+  g.ldaux = ldaux; g.accumulate = c.accumulate; g.alpha = 1.0f; g.alpha_dev = nullptr;
   int rc = hs_gemm(&g, nullptr);
   if (rc) { printf("FAIL %-28s launch error: %s\n", c.name, hs_last_error()); return 1; }
   cudaError_t e = cudaDeviceSynchronize();

@@ -36,7 +36,7 @@ class GemmArgs(ctypes.Structure):
         ('in_dtype', ctypes.c_int), ('out_dtype', ctypes.c_int),
         ('bias', ctypes.c_void_p), ('act', ctypes.c_int),
         ('aux_out', ctypes.c_void_p), ('aux_in', ctypes.c_void_p), ('ldaux', ctypes.c_int),
-        ('accumulate', ctypes.c_int), ('alpha', ctypes.c_float),
+        ('accumulate', ctypes.c_int), ('alpha', ctypes.c_float), ('alpha_dev', ctypes.c_void_p),
     ]
 
 
@@ -58,6 +58,10 @@ def load() -> ctypes.CDLL:
     lib.hs_last_error.restype = ctypes.c_char_p
     lib.hs_version.restype = ctypes.c_int
     lib.hs_launch_count.restype = ctypes.c_uint64
+    for fn in ('hs_sumsq_scratch_elems',):
+        getattr(lib, fn).restype = ctypes.c_int
+    lib.hs_ln_bwd_scratch_elems.argtypes = [ctypes.c_int, ctypes.c_int]
+    lib.hs_colsum_scratch_elems.argtypes = [ctypes.c_int, ctypes.c_int]
     _declare(lib)
     _lib = lib
     return lib

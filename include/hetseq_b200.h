@@ -64,11 +64,84 @@ typedef struct hs_gemm_args {
   int ldaux;
   int accumulate;   /* 1: C += result (read-modify-write); used by wgrad into the flat grad buffer */
   float alpha;      /* scales the accumulator before bias/activation */
+  const float* alpha_dev; /* optional device scalar multiplied into alpha (e.g. the upstream loss gradient) */
 } hs_gemm_args;
 
 /* Replaces F.linear/cuBLAS at bert_modeling.py:352-354,387-391,409-413,423-427,514-515,525-528,547
  * and the autograd GEMMs behind them (SURVEY.md K1,K5-K7,K9-K11,K14). */
 HS_API int hs_gemm(const hs_gemm_args* args, hs_stream_t stream);
+
+/* ---- flat-buffer gradient norm + fused optimizer updates (csrc/optim_sm100.cu) ------------------- */
+/* "Owned" elements: chunk c covers [c*stride, c*stride+chunk) of the flat gradient/parameter buffers;
+ * optimizer state and fp32 master weights are compact (c*chunk + i). chunk, stride: multiples of 8. */
+
+/* Number of floats of scratch hs_sumsq needs (per call; contents are overwritten). */
+HS_API int hs_sumsq_scratch_elems(void);
+/* out[0] (= or +=) sum of squares of the owned gradient elements. Two deterministic stages: block
+ * partials into `scratch`, then one block reduces them. Replaces the norm loop of optim.py:65-70. */
+HS_API int hs_sumsq(const void* grad, int dtype, long long nchunks, int chunk, long long stride,
+                    float* scratch, float* out, int accumulate, hs_stream_t stream);
+/* fairseq Adam on flat memory, math of optim.py:162-231 (decoupled decay before the update, bias
+ * correction via step_factor = sqrt(1-b2^t)/(1-b1^t), eps outside the sqrt). The gradient is read
+ * once and multiplied by mult_host * (*mult_dev) on the fly -- this is where multiply_grads
+ * (optim.py:59-63), the clip coefficient and 1/loss_scale are applied. hyper_dev = [lr, step_factor]
+ * overrides the host values when non-NULL; *skip_dev != 0 makes the call a no-op (overflow step). */
+HS_API int hs_adam_flat(const float* grad, float* master, float* exp_avg, float* exp_avg_sq, void* param_out,
+                        int out_dtype, long long nchunks, int chunk, long long stride, float lr, float beta1,
+                        float beta2, float eps, float weight_decay, float step_factor, float mult_host,
+                        const float* mult_dev, const float* hyper_dev, const int* skip_dev, hs_stream_t stream);
+/* Adadelta with coupled L2 decay, math of optim.py:263-304; same conventions as hs_adam_flat. */
+HS_API int hs_adadelta_flat(const float* grad, float* master, float* square_avg, float* acc_delta,
+                            void* param_out, int out_dtype, long long nchunks, int chunk, long long stride,
+                            float lr, float rho, float eps, float weight_decay, float mult_host,
+                            const float* mult_dev, const float* hyper_dev, const int* skip_dev,
+                            hs_stream_t stream);
+
+/* ---- fused (bias +) dropout + residual + LayerNorm (csrc/layernorm_sm100.cu) --------------------- */
+/* z = residual + dropout(x + bias); y = gamma*(z-mean)/sqrt(var+eps)+beta, TF-style (eps inside the
+ * sqrt, biased variance: bert_modeling.py:277-289). post_dropout=1 instead computes y = dropout(LN(x))
+ * (the embeddings, bert_modeling.py:313-319). bias/residual/z/mean/rstd may be NULL. Dropout masks are
+ * Philox(seed[0..1], site, element) and are recomputed by hs_ln_bwd. H % 8 == 0, H <= 2048.
+ * Replaces the dropout + add + ~9 LayerNorm launches of bert_modeling.py:387-391,423-427 (K5,K7,W5,W7). */
+HS_API int hs_ln_fwd(const void* x, const void* bias, const void* residual, const void* gamma, const void* beta,
+                     void* y, void* z, float* mean, float* rstd, int M, int H, float eps, float dropout_p,
+                     const long long* seed, unsigned site, int post_dropout, int dtype, hs_stream_t stream);
+HS_API int hs_ln_bwd_scratch_elems(int M, int H);
+/* dz = dLN/dz (residual path), dx = dz * dropout mask (GEMM path, may be NULL), dgamma/dbeta fp32
+ * (= or += per accumulate_params) via per-block partials in `scratch` + a deterministic second stage. */
+HS_API int hs_ln_bwd(const void* dy, const void* z, const void* gamma, const float* mean, const float* rstd,
+                     void* dz, void* dx, float* dgamma, float* dbeta, int accumulate_params, float* scratch,
+                     int M, int H, float dropout_p, const long long* seed, unsigned site, int post_dropout,
+                     int dtype, hs_stream_t stream);
+HS_API int hs_colsum_scratch_elems(int M, int N);
+/* out[n] (= or +=) sum_m x[m,n] for a 16-bit [M,N] matrix: the bias gradients of every Linear. */
+HS_API int hs_colsum(const void* x, int M, int N, int ld, float* out, int accumulate, float* scratch, int dtype,
+                     hs_stream_t stream);
+
+/* ---- fused cross-entropy + MLM row gather/scatter (csrc/xent_sm100.cu) ------------------------------- */
+/* CrossEntropyLoss(ignore_index=-1), mean reduction (bert_modeling.py:881-886, K13). Per row: online
+ * log-sum-exp, row_loss[r]; with write_grad the logits are overwritten in place by
+ * (softmax - onehot) / n_valid (ignored rows and pad columns [V, ld) become 0). loss (optional)
+ * (= or +=) mean over valid rows. labels int32 or int64. */
+HS_API int hs_xent(void* logits, int ld, const void* labels, int label_is_i64, int rows, int V, float* row_loss,
+                   float* loss, int accumulate_loss, int write_grad, int dtype, hs_stream_t stream);
+/* dst[r,:] = src[idx[r],:] (idx < 0 -> zeros): only the labelled positions enter the MLM head (Q21/W9). */
+HS_API int hs_gather_rows(const void* src, const void* idx, int idx_is_i64, void* dst, int rows, int row_bytes,
+                          hs_stream_t stream);
+/* dst[idx[r],:] += src[r,:] for unique valid idx (gradient of hs_gather_rows). */
+HS_API int hs_scatter_add_rows(const void* src, const void* idx, int idx_is_i64, void* dst, int rows, int H,
+                               int dtype, hs_stream_t stream);
+
+/* ---- embeddings (csrc/embedding_sm100.cu; bert_modeling.py:292-320, K8/W8) --------------------------- */
+HS_API int hs_embed_gather_sum(const void* W, const void* P, const void* Tt, const void* ids, const void* seg,
+                               int ids_i64, void* z, int M, int S, int H, int vocab, int ntypes, int dtype,
+                               hs_stream_t stream);
+HS_API int hs_embed_scatter_word(const void* de, const void* ids, int ids_i64, float* dW, int M, int H, int vocab,
+                                 int dtype, hs_stream_t stream);
+HS_API int hs_sum_over_batch(const void* x, int B, long long inner, float* out, int accumulate, int dtype,
+                             hs_stream_t stream);
+HS_API int hs_colsum_rows_where(const void* x, const void* sel, int sel_i64, long long want, int M, int N, float* out,
+                                int accumulate, float* scratch, int dtype, hs_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,224 @@
+"""GPU numerics: every native kernel against a plain PyTorch fp32 restatement of the same op."""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+DT = [torch.float16, torch.bfloat16]
+
+
+def tol(dt):
+    return dict(rtol=2e-2, atol=2e-2) if dt == torch.bfloat16 else dict(rtol=4e-3, atol=4e-3)
+
+
+@pytest.fixture(scope='module')
+def nat():
+    from hetseq_b200.ops import lib, native
+    lib.load()
+    return native
+
+
+def gelu_ref(x):
+    return x * 0.5 * (1.0 + torch.erf(x / 1.41421))
+
+
+@pytest.mark.parametrize('dt', DT)
+@pytest.mark.parametrize('shape', [(256, 512, 256), (200, 264, 136), (4096, 1024, 1024)])
+def test_gemm_forward_bias_gelu(nat, dt, shape):
+    M, N, K = shape
+    torch.manual_seed(0)
+    x = (torch.randn(M, K, device='cuda') * 0.5).to(dt)
+    w = (torch.randn(N, K, device='cuda') * 0.05).to(dt)
+    b = torch.randn(N, device='cuda').to(dt)
+    y = torch.empty(M, N, dtype=dt, device='cuda')
+    pre = torch.empty(M, N, dtype=dt, device='cuda')
+    nat.gemm(x, w, y, M, N, K, lda=K, ldb=K, ldc=N, bias=b, act=nat.ACT_GELU, aux_out=pre, ldaux=N)
+    ref_pre = x.float() @ w.float().t() + b.float()
+    torch.testing.assert_close(pre.float(), ref_pre, **tol(dt))
+    torch.testing.assert_close(y.float(), gelu_ref(ref_pre), **tol(dt))
+
+
+@pytest.mark.parametrize('dt', DT)
+def test_gemm_dgrad_wgrad(nat, dt):
+    M, N, K = 512, 384, 640
+    torch.manual_seed(1)
+    x = (torch.randn(M, K, device='cuda') * 0.5).to(dt)
+    w = (torch.randn(N, K, device='cuda') * 0.05).to(dt)
+    dy = (torch.randn(M, N, device='cuda') * 0.1).to(dt)
+    dx = torch.empty(M, K, dtype=dt, device='cuda')
+    nat.gemm(dy, w, dx, M, K, N, lda=N, ldb=K, ldc=K, b_mn=True)
+    torch.testing.assert_close(dx.float(), dy.float() @ w.float(), **tol(dt))
+    dw = torch.full((N, K), 0.25, dtype=torch.float32, device='cuda')
+    nat.gemm(dy, x, dw, N, K, M, lda=N, ldb=K, ldc=K, a_mn=True, b_mn=True, accumulate=True)
+    torch.testing.assert_close(dw, dy.float().t() @ x.float() + 0.25, rtol=2e-3, atol=2e-3)
+    g = torch.tensor([3.0], device='cuda')
+    nat.gemm(dy, x, dw, N, K, M, lda=N, ldb=K, ldc=K, a_mn=True, b_mn=True, alpha_dev=g)
+    torch.testing.assert_close(dw, 3 * (dy.float().t() @ x.float()), rtol=2e-3, atol=4e-3)
+
+
+@pytest.mark.parametrize('dt', DT)
+def test_gemm_dgelu_epilogue(nat, dt):
+    M, N, K = 256, 512, 384
+    torch.manual_seed(2)
+    df = (torch.randn(M, K, device='cuda') * 0.1).to(dt)
+    w2 = (torch.randn(K, N, device='cuda') * 0.05).to(dt)      # [H_out, I] row-major: dPre = dF @ W2
+    pre = torch.randn(M, N, device='cuda').to(dt)
+    out = torch.empty(M, N, dtype=dt, device='cuda')
+    nat.gemm(df, w2, out, M, N, K, lda=K, ldb=N, ldc=N, b_mn=True, act=nat.ACT_DGELU_MUL, aux_in=pre, ldaux=N)
+    p = pre.float().requires_grad_(True)
+    gelu_ref(p).backward(df.float() @ w2.float())
+    torch.testing.assert_close(out.float(), p.grad, **tol(dt))
+
+
+@pytest.mark.parametrize('dt', DT)
+@pytest.mark.parametrize('H', [256, 768, 1024])
+@pytest.mark.parametrize('p', [0.0, 0.1])
+def test_layernorm_fwd_bwd(nat, dt, H, p):
+    from hetseq_b200.ops import rng
+    M = 300
+    torch.manual_seed(3)
+    x = torch.randn(M, H, device='cuda').to(dt)
+    res = torch.randn(M, H, device='cuda').to(dt)
+    gamma = (1 + 0.1 * torch.randn(H, device='cuda')).to(dt)
+    beta = (0.1 * torch.randn(H, device='cuda')).to(dt)
+    rng.set_step_seed(1234, 0)
+    seed = rng.seed_tensor(torch.device('cuda', 0))
+    y, z, mean, rstd = nat.ln_fwd(x, None, res, gamma, beta, p=p, seed=seed, site=7)
+    # recover the mask from z: z = res + mask*x/(1-p)
+    if p > 0:
+        keep = ((z.float() - res.float()).abs() > 0) | (x.float().abs() < 1e-6)
+        frac = keep.float().mean().item()
+        assert abs(frac - (1 - p)) < 0.02
+        y2, z2, _, _ = nat.ln_fwd(x, None, res, gamma, beta, p=p, seed=seed, site=7)
+        assert torch.equal(z, z2), 'dropout mask must be a pure function of (seed, site, index)'
+        _, z3, _, _ = nat.ln_fwd(x, None, res, gamma, beta, p=p, seed=seed, site=8)
+        assert not torch.equal(z, z3)
+        mask = keep.float() / (1 - p)
+    else:
+        mask = torch.ones(M, H, device='cuda')
+    xr, rr = x.float().requires_grad_(True), res.float().requires_grad_(True)
+    g32, b32 = gamma.float().requires_grad_(True), beta.float().requires_grad_(True)
+    zr = rr + xr * mask
+    u = zr.mean(-1, keepdim=True)
+    s = (zr - u).pow(2).mean(-1, keepdim=True)
+    yr = g32 * ((zr - u) / torch.sqrt(s + 1e-12)) + b32
+    torch.testing.assert_close(y.float(), yr, **tol(dt))
+    dy = torch.randn(M, H, device='cuda').to(dt)
+    yr.backward(dy.float())
+    dgamma = torch.zeros(H, device='cuda')
+    dbeta = torch.full((H,), 0.5, device='cuda')
+    dz, dx = nat.ln_bwd(dy, z, gamma, mean, rstd, dgamma, dbeta, False, p=p, seed=seed, site=7)
+    t = dict(rtol=3e-2, atol=3e-2) if dt == torch.bfloat16 else dict(rtol=1e-2, atol=1e-2)
+    torch.testing.assert_close(dz.float(), rr.grad, **t)
+    torch.testing.assert_close(dx.float(), xr.grad, **t)
+    torch.testing.assert_close(dgamma, g32.grad, rtol=2e-2, atol=5e-2)
+    torch.testing.assert_close(dbeta, b32.grad, rtol=2e-2, atol=5e-2)
+
+
+@pytest.mark.parametrize('dt', DT)
+@pytest.mark.parametrize('V', [2, 1000, 30522])
+def test_xent(nat, dt, V):
+    rows = 37
+    torch.manual_seed(4)
+    ld = (V + 127) // 128 * 128 if V > 128 else 8
+    logits = torch.zeros(rows, ld, dtype=dt, device='cuda')
+    logits[:, :V] = (torch.randn(rows, V, device='cuda') * 3).to(dt)
+    labels = torch.randint(0, V, (rows,), device='cuda', dtype=torch.int32)
+    labels[::5] = -1
+    ref_in = logits[:, :V].float().requires_grad_(True)
+    ref = F.cross_entropy(ref_in, labels.long(), ignore_index=-1)
+    ref.backward()
+    loss = torch.zeros(1, device='cuda')
+    nat.xent(logits, ld, labels, rows, V, loss, False)
+    torch.testing.assert_close(loss[0], ref.detach(), rtol=1e-4, atol=1e-4)
+    torch.testing.assert_close(logits[:, :V].float(), ref_in.grad, rtol=2e-2, atol=1e-3 if dt == torch.float16 else 4e-3)
+    assert torch.count_nonzero(logits[:, V:]) == 0
+
+
+@pytest.mark.parametrize('dt', DT)
+def test_colsum_gather_scatter(nat, dt):
+    M, N = 1000, 776
+    torch.manual_seed(5)
+    x = torch.randn(M, N, device='cuda').to(dt)
+    out = torch.ones(N, device='cuda')
+    nat.colsum(x, M, N, N, out, True)
+    torch.testing.assert_close(out, x.float().sum(0) + 1, rtol=1e-3, atol=2e-2)
+    src = torch.randn(500, 256, device='cuda').to(dt)
+    idx = torch.randperm(500, device='cuda')[:64].to(torch.int32)
+    g = nat.gather_rows(src, idx, 64)
+    assert torch.equal(g, src[idx.long()])
+    dst = torch.zeros(500, 256, dtype=dt, device='cuda')
+    nat.scatter_add_rows(g, idx, dst)
+    ref = torch.zeros(500, 256, dtype=dt, device='cuda')
+    ref[idx.long()] = g
+    assert torch.equal(dst, ref)
+
+
+@pytest.mark.parametrize('dt', DT)
+def test_embedding_kernels(nat, dt):
+    B, S, H, V = 4, 32, 256, 1000
+    torch.manual_seed(6)
+    W = torch.randn(V, H, device='cuda').to(dt)
+    P = torch.randn(64, H, device='cuda').to(dt)
+    T = torch.randn(2, H, device='cuda').to(dt)
+    ids = torch.randint(0, V, (B * S,), device='cuda', dtype=torch.int32)
+    seg = torch.randint(0, 2, (B * S,), device='cuda', dtype=torch.int32)
+    z = nat.embed_gather_sum(W, P, T, ids, seg, B * S, S)
+    pos = torch.arange(S, device='cuda').repeat(B)
+    ref = W[ids.long()].float() + P[pos].float() + T[seg.long()].float()
+    torch.testing.assert_close(z.float(), ref, **tol(dt))
+    de = torch.randn(B * S, H, device='cuda').to(dt)
+    dW = torch.zeros(V, H, device='cuda')
+    nat.embed_scatter_word(de, ids, dW)
+    refW = torch.zeros(V, H, device='cuda').index_add_(0, ids.long(), de.float())
+    torch.testing.assert_close(dW, refW, rtol=1e-4, atol=1e-4)
+    dP = torch.zeros(S * H, device='cuda')
+    nat.sum_over_batch(de, B, S * H, dP, False)
+    torch.testing.assert_close(dP.view(S, H), de.float().view(B, S, H).sum(0), rtol=1e-4, atol=1e-4)
+    dT = torch.zeros(2, H, device='cuda')
+    for t in range(2):
+        nat.colsum_rows_where(de, seg, t, dT[t], False)
+    refT = torch.zeros(2, H, device='cuda').index_add_(0, seg.long(), de.float())
+    torch.testing.assert_close(dT, refT, rtol=1e-4, atol=1e-3)
+
+
+@pytest.mark.parametrize('kind', ['adam', 'adadelta'])
+@pytest.mark.parametrize('dt', [torch.float16, torch.float32])
+def test_fused_optimizer_matches_per_tensor(kind, dt):
+    """Flat native update == the reference's per-tensor math (optim/tensor_optimizers.py)."""
+    from hetseq_b200 import options
+    from hetseq_b200.optim import Adam, Adadelta, _Adam, _Adadelta
+    torch.manual_seed(7)
+    shapes = [(300, 70), (1000,), (64, 64), (5,)]
+    ref_params = [torch.nn.Parameter(torch.randn(s, device='cuda')) for s in shapes]
+    params = [torch.nn.Parameter(p.detach().clone().to(dt)) for p in ref_params]
+    for p, q in zip(ref_params, params):
+        p.data.copy_(q.data.float())
+    args = options.make_args('mnist', kind, argv=['--lr', '0.01'] + (['--weight-decay', '0.1'] if kind == 'adam' else []))
+    args.kernels = 'native'
+    opt = (_Adam if kind == 'adam' else _Adadelta)(args, params)
+    assert opt._native is not None
+    ref = Adam(ref_params, lr=0.01, weight_decay=0.1) if kind == 'adam' else Adadelta(ref_params, lr=0.01)
+    for step in range(3):
+        opt.zero_grad()
+        for p, q in zip(ref_params, params):
+            g = torch.randn_like(p)
+            p.grad = g.clone() * 0.5
+            q.main_grad.copy_(g)
+        opt.multiply_grads(0.5)
+        gn = opt.clip_grad_norm(0.0)
+        ref_norm = math.sqrt(sum(float(p.grad.pow(2).sum()) for p in ref_params))
+        assert abs(float(gn) - ref_norm) / ref_norm < 1e-4
+        opt.step()
+        ref.step()
+    for p, q in zip(ref_params, params):
+        if dt == torch.float32:
+            torch.testing.assert_close(q.data, p.data, rtol=1e-5, atol=1e-6)
+        else:
+            torch.testing.assert_close(q.data.float(), p.data, rtol=2e-3, atol=2e-3)
+    # fp32 master stays exact even for fp16 params
+    i = 0
+    torch.testing.assert_close(opt.master[:ref_params[0].numel()].view(shapes[0]), ref_params[0].data, rtol=1e-5, atol=1e-6)
