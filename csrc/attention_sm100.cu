@@ -1,0 +1,439 @@
+// hetseq_b200 -- fused masked-softmax attention on tcgen05 (forward and backward), head_dim 64.
+//
+// Reference: BertSelfAttention.forward (bert_modeling.py:351-377): scores = Q K^T / sqrt(d) + mask,
+// softmax, dropout on the probabilities, P V, head merge -- six library launches that materialise the
+// [B,h,S,S] score tensor three times. Here one CTA owns one (batch, head) pair:
+//
+//   forward   TMA: Q,K,V tiles [128 x 64] straight out of the packed [M,3H] projection (no head-split
+//             copy) -> tcgen05.mma S = Q K^T into TMEM -> each of 128 threads owns one query row:
+//             scale + additive mask + softmax + Philox dropout in registers -> P (16-bit) to swizzled
+//             smem -> tcgen05.mma O = P V -> normalise, write [M,H] at the head's columns (head merge
+//             for free) + log-sum-exp per row.
+//   backward  S and dP = dO V^T by tcgen05 -> per row: P = exp(s - lse), the same dropout mask recomputed,
+//             dS = P (dP - rowsum(dO O)) / sqrt(d) -> P and dS staged once in smem and consumed three
+//             times through different UMMA descriptors (K-major for dQ = dS K, MN-major for
+//             dV = P^T dO and dK = dS^T Q) -> dQ,dK,dV written into the packed [M,3H] gradient.
+//
+// The score matrix never leaves the SM. Sequence length 128 per tile (BERT phase 1); other lengths
+// are reported as unsupported by hs_attention_supported() and the caller must not use this kernel.
+#include "common.cuh"
+#include "host.h"
+#include "../include/hetseq_b200.h"
+
+#include <type_traits>
+
+namespace hs {
+
+constexpr int AT_S = 128;   // queries and keys per tile
+constexpr int AT_D = 64;    // head dim
+constexpr int AT_THREADS = 128;
+constexpr int TILE_BYTES = AT_S * 128;       // [128 rows x 64 x 16-bit], 128B rows, SW128
+constexpr int PBUF_BYTES = 2 * TILE_BYTES;   // [128 x 128] 16-bit as two 64-column SW128 regions
+
+struct AttnParams {
+  const float* mask;      // [B, S] additive
+  void* out;              // fwd: ctx [M, H];  bwd: dqkv [M, 3H]
+  const void* o;          // bwd: forward output [M, H]
+  const void* dout;       // bwd: dO [M, H] (also via tensor map)
+  float* lse;             // [B*heads*S]
+  int B, heads, H;
+  float scale, p;
+  const long long* seed;
+  uint32_t site;
+};
+
+__device__ __forceinline__ uint32_t sw128_offset(int row, int col16 /*16-byte chunk 0..7*/) {
+  return static_cast<uint32_t>(row * 128 + ((col16 ^ (row & 7)) << 4));
+}
+
+// keep-scale for 4 consecutive key columns of one query row
+__device__ __forceinline__ void drop4(const long long* seed_ptr, uint32_t site, uint64_t e0, float p, float inv,
+                                      float (&mk)[4]) {
+  const uint64_t seed = static_cast<uint64_t>(seed_ptr[0]) * 0x9E3779B97F4A7C15ull + static_cast<uint64_t>(seed_ptr[1]);
+  const float4 r = philox_uniform4(seed, site, e0 >> 2);
+  mk[0] = r.x >= p ? inv : 0.f; mk[1] = r.y >= p ? inv : 0.f;
+  mk[2] = r.z >= p ? inv : 0.f; mk[3] = r.w >= p ? inv : 0.f;
+}
+
+template <typename T>
+__device__ __forceinline__ void store_row_chunk8(uint8_t* buf, int row, int col0, const float (&v)[8]) {
+  // 8 consecutive columns starting at col0 (multiple of 8) of a [128 x 128] two-region SW128 buffer
+  const int region = col0 >> 6, c16 = (col0 & 63) >> 3;
+  uint4 u;
+  u.x = Cvt<T>::pack2(v[0], v[1]); u.y = Cvt<T>::pack2(v[2], v[3]);
+  u.z = Cvt<T>::pack2(v[4], v[5]); u.w = Cvt<T>::pack2(v[6], v[7]);
+  *reinterpret_cast<uint4*>(buf + region * TILE_BYTES + sw128_offset(row, c16)) = u;
+}
+
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(AT_THREADS, 2)
+attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams P) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;
+  uint8_t* sK = sQ + TILE_BYTES;
+  uint8_t* sV = sK + TILE_BYTES;
+  uint8_t* sP = sV + TILE_BYTES;
+  float* sMask = reinterpret_cast<float*>(sP + PBUF_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sMask + AT_S);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int b = blockIdx.x / P.heads, h = blockIdx.x % P.heads;
+  const int row0 = b * AT_S;
+
+  if (tid == 0) {
+    tma_prefetch_desc(&tmQKV);
+    mbar_init(&bars[0], 1);
+    mbar_init(&bars[1], 1);
+    mbar_init(&bars[2], 1);
+    fence_mbar_init();
+  }
+  if (warp == 0) {
+    __syncwarp();
+    tmem_alloc(tmem_slot, 256);
+  }
+  sMask[tid] = P.mask[b * AT_S + tid];
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (tid == 0) {
+    mbar_expect_tx(&bars[0], 3 * TILE_BYTES);
+    tma_load_2d(sQ, &tmQKV, &bars[0], h * AT_D, row0);
+    tma_load_2d(sK, &tmQKV, &bars[0], P.H + h * AT_D, row0);
+    tma_load_2d(sV, &tmQKV, &bars[0], 2 * P.H + h * AT_D, row0);
+    mbar_wait(&bars[0], 0);
+    tc_fence_after();
+    // S[q,k] = Q K^T : M=128, N=128, K=64
+    const uint32_t idesc = umma_idesc_f16(sizeof(T) == 2 && std::is_same<T, __nv_bfloat16>::value ? 1 : 0, 0, 0, 128, 128);
+    const uint64_t aq = umma_desc_sw128(smem_u32(sQ), 16, 1024);
+    const uint64_t bk = umma_desc_sw128(smem_u32(sK), 16, 1024);
+#pragma unroll
+    for (int k = 0; k < AT_D / 16; ++k) umma_f16(tmem, aq + k * 2, bk + k * 2, idesc, k != 0);
+    umma_commit(&bars[1]);
+  }
+  mbar_wait(&bars[1], 0);
+  __syncwarp();
+  tc_fence_after();
+
+  // ---- softmax: thread `tid` owns query row `tid` ----
+  const uint32_t t_row = tmem + (static_cast<uint32_t>(warp * 32) << 16);
+  const float sl2 = P.scale * 1.4426950408889634f;   // fold log2(e) into the scale
+  float s[AT_S];
+#pragma unroll
+  for (int c = 0; c < AT_S / 32; ++c) {
+    uint32_t r[32];
+    tmem_ld_32x32(t_row + c * 32, r);
+    tmem_ld_wait();
+#pragma unroll
+    for (int i = 0; i < 32; ++i) s[c * 32 + i] = __uint_as_float(r[i]) * sl2 + sMask[c * 32 + i] * 1.4426950408889634f;
+  }
+  float mx = -INFINITY;
+#pragma unroll
+  for (int i = 0; i < AT_S; ++i) mx = fmaxf(mx, s[i]);
+  float l = 0.f;
+#pragma unroll
+  for (int i = 0; i < AT_S; ++i) { s[i] = exp2f(s[i] - mx); l += s[i]; }
+  const bool drop = P.p > 0.f;
+  const float inv_keep = drop ? 1.f / (1.f - P.p) : 1.f;
+  const uint64_t e_row = (static_cast<uint64_t>(blockIdx.x) * AT_S + tid) * AT_S;
+#pragma unroll
+  for (int c8 = 0; c8 < AT_S / 8; ++c8) {
+    float v[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[i] = s[c8 * 8 + i];
+    if (drop) {
+      float m0[4], m1[4];
+      drop4(P.seed, P.site, e_row + c8 * 8, P.p, inv_keep, m0);
+      drop4(P.seed, P.site, e_row + c8 * 8 + 4, P.p, inv_keep, m1);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) { v[i] *= m0[i]; v[4 + i] *= m1[i]; }
+    }
+    store_row_chunk8<T>(sP, tid, c8 * 8, v);
+  }
+  if (P.lse) P.lse[static_cast<size_t>(blockIdx.x) * AT_S + tid] = (mx + log2f(l)) * 0.6931471805599453f;
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+
+  if (tid == 0) {
+    tc_fence_after();
+    // O[q,d] = P V : M=128, N=64, K=128; A = P (K-major, two 64-wide k regions), B = V (MN-major)
+    const int fmt = std::is_same<T, __nv_bfloat16>::value ? 1 : 0;
+    const uint32_t idesc = umma_idesc_f16(fmt, 0, 1, 128, 64);
+#pragma unroll
+    for (int kk = 0; kk < AT_S / 16; ++kk) {
+      const uint64_t ap = umma_desc_sw128(smem_u32(sP) + (kk >> 2) * TILE_BYTES + (kk & 3) * 32, 16, 1024);
+      const uint64_t bv = umma_desc_sw128(smem_u32(sV) + kk * 2048, TILE_BYTES, 1024);
+      umma_f16(tmem + 128, ap, bv, idesc, kk != 0);
+    }
+    umma_commit(&bars[2]);
+  }
+  mbar_wait(&bars[2], 0);
+  __syncwarp();
+  tc_fence_after();
+  {
+    const float inv_l = 1.f / l;
+    T* dst = reinterpret_cast<T*>(P.out) + static_cast<size_t>(row0 + tid) * P.H + h * AT_D;
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      uint32_t r[32];
+      tmem_ld_32x32(t_row + 128 + c * 32, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        uint4 u;
+        u.x = Cvt<T>::pack2(__uint_as_float(r[i * 8 + 0]) * inv_l, __uint_as_float(r[i * 8 + 1]) * inv_l);
+        u.y = Cvt<T>::pack2(__uint_as_float(r[i * 8 + 2]) * inv_l, __uint_as_float(r[i * 8 + 3]) * inv_l);
+        u.z = Cvt<T>::pack2(__uint_as_float(r[i * 8 + 4]) * inv_l, __uint_as_float(r[i * 8 + 5]) * inv_l);
+        u.w = Cvt<T>::pack2(__uint_as_float(r[i * 8 + 6]) * inv_l, __uint_as_float(r[i * 8 + 7]) * inv_l);
+        reinterpret_cast<uint4*>(dst + c * 32)[i] = u;
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc(tmem, 256);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(AT_THREADS, 1)
+attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
+                const AttnParams P) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;
+  uint8_t* sK = sQ + TILE_BYTES;
+  uint8_t* sV = sK + TILE_BYTES;
+  uint8_t* sDO = sV + TILE_BYTES;
+  uint8_t* sP = sDO + TILE_BYTES;
+  uint8_t* sDS = sP + PBUF_BYTES;
+  float* sMask = reinterpret_cast<float*>(sDS + PBUF_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sMask + AT_S);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3);
+
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int b = blockIdx.x / P.heads, h = blockIdx.x % P.heads;
+  const int row0 = b * AT_S;
+  const int fmt = std::is_same<T, __nv_bfloat16>::value ? 1 : 0;
+
+  if (tid == 0) {
+    tma_prefetch_desc(&tmQKV);
+    tma_prefetch_desc(&tmDO);
+    mbar_init(&bars[0], 1);
+    mbar_init(&bars[1], 1);
+    mbar_init(&bars[2], 1);
+    fence_mbar_init();
+  }
+  if (warp == 0) {
+    __syncwarp();
+    tmem_alloc(tmem_slot, 512);
+  }
+  sMask[tid] = P.mask[b * AT_S + tid];
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  // TMEM columns: S [0,128)  dP [128,256)  dV [256,320)  dK [320,384)  dQ [384,448)
+
+  if (tid == 0) {
+    mbar_expect_tx(&bars[0], 4 * TILE_BYTES);
+    tma_load_2d(sQ, &tmQKV, &bars[0], h * AT_D, row0);
+    tma_load_2d(sK, &tmQKV, &bars[0], P.H + h * AT_D, row0);
+    tma_load_2d(sV, &tmQKV, &bars[0], 2 * P.H + h * AT_D, row0);
+    tma_load_2d(sDO, &tmDO, &bars[0], h * AT_D, row0);
+    mbar_wait(&bars[0], 0);
+    tc_fence_after();
+    const uint32_t idesc = umma_idesc_f16(fmt, 0, 0, 128, 128);
+    const uint64_t aq = umma_desc_sw128(smem_u32(sQ), 16, 1024);
+    const uint64_t bk = umma_desc_sw128(smem_u32(sK), 16, 1024);
+    const uint64_t ado = umma_desc_sw128(smem_u32(sDO), 16, 1024);
+    const uint64_t bv = umma_desc_sw128(smem_u32(sV), 16, 1024);
+#pragma unroll
+    for (int k = 0; k < AT_D / 16; ++k) umma_f16(tmem, aq + k * 2, bk + k * 2, idesc, k != 0);          // S = Q K^T
+#pragma unroll
+    for (int k = 0; k < AT_D / 16; ++k) umma_f16(tmem + 128, ado + k * 2, bv + k * 2, idesc, k != 0);   // dP = dO V^T
+    umma_commit(&bars[1]);
+  }
+
+  // while the MMAs run: D = rowsum(dO * O) for this thread's query row, straight from global memory
+  float Dq = 0.f;
+  {
+    const T* o = reinterpret_cast<const T*>(P.o) + static_cast<size_t>(row0 + tid) * P.H + h * AT_D;
+    const T* d = reinterpret_cast<const T*>(P.dout) + static_cast<size_t>(row0 + tid) * P.H + h * AT_D;
+#pragma unroll
+    for (int i = 0; i < AT_D / 8; ++i) {
+      const uint4 uo = reinterpret_cast<const uint4*>(o)[i], ud = reinterpret_cast<const uint4*>(d)[i];
+      const float2 o0 = Cvt<T>::unpack2(uo.x), o1 = Cvt<T>::unpack2(uo.y), o2 = Cvt<T>::unpack2(uo.z), o3 = Cvt<T>::unpack2(uo.w);
+      const float2 d0 = Cvt<T>::unpack2(ud.x), d1 = Cvt<T>::unpack2(ud.y), d2 = Cvt<T>::unpack2(ud.z), d3 = Cvt<T>::unpack2(ud.w);
+      Dq += o0.x * d0.x + o0.y * d0.y + o1.x * d1.x + o1.y * d1.y + o2.x * d2.x + o2.y * d2.y + o3.x * d3.x + o3.y * d3.y;
+    }
+  }
+  const float lse2 = P.lse[static_cast<size_t>(blockIdx.x) * AT_S + tid] * 1.4426950408889634f;
+  mbar_wait(&bars[1], 0);
+  __syncwarp();
+  tc_fence_after();
+
+  const uint32_t t_row = tmem + (static_cast<uint32_t>(warp * 32) << 16);
+  const float sl2 = P.scale * 1.4426950408889634f;
+  const bool drop = P.p > 0.f;
+  const float inv_keep = drop ? 1.f / (1.f - P.p) : 1.f;
+  const uint64_t e_row = (static_cast<uint64_t>(blockIdx.x) * AT_S + tid) * AT_S;
+#pragma unroll 1
+  for (int c = 0; c < AT_S / 32; ++c) {
+    uint32_t rs[32], rd[32];
+    tmem_ld_32x32(t_row + c * 32, rs);
+    tmem_ld_32x32(t_row + 128 + c * 32, rd);
+    tmem_ld_wait();
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      float pv[8], dsv[8], mk[8];
+      if (drop) {
+        float m0[4], m1[4];
+        drop4(P.seed, P.site, e_row + c * 32 + g * 8, P.p, inv_keep, m0);
+        drop4(P.seed, P.site, e_row + c * 32 + g * 8 + 4, P.p, inv_keep, m1);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { mk[i] = m0[i]; mk[4 + i] = m1[i]; }
+      } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) mk[i] = 1.f;
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int col = c * 32 + g * 8 + i;
+        const float p = exp2f(__uint_as_float(rs[g * 8 + i]) * sl2 + sMask[col] * 1.4426950408889634f - lse2);
+        const float dp = __uint_as_float(rd[g * 8 + i]) * mk[i];
+        pv[i] = p * mk[i];                        // dropped probabilities (what multiplied V in forward)
+        dsv[i] = p * (dp - Dq) * P.scale;         // d(scores) including the 1/sqrt(d)
+      }
+      store_row_chunk8<T>(sP, tid, c * 32 + g * 8, pv);
+      store_row_chunk8<T>(sDS, tid, c * 32 + g * 8, dsv);
+    }
+  }
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+
+  if (tid == 0) {
+    tc_fence_after();
+    const uint32_t id_mm = umma_idesc_f16(fmt, 1, 1, 128, 64);   // A MN-major, B MN-major
+    const uint32_t id_km = umma_idesc_f16(fmt, 0, 1, 128, 64);   // A K-major,  B MN-major
+#pragma unroll
+    for (int kk = 0; kk < AT_S / 16; ++kk) {
+      // reduction over queries: 16 query rows per step = 2048 B in every operand
+      const uint64_t aP = umma_desc_sw128(smem_u32(sP) + kk * 2048, TILE_BYTES, 1024);
+      const uint64_t aDS = umma_desc_sw128(smem_u32(sDS) + kk * 2048, TILE_BYTES, 1024);
+      const uint64_t bDO = umma_desc_sw128(smem_u32(sDO) + kk * 2048, TILE_BYTES, 1024);
+      const uint64_t bQ = umma_desc_sw128(smem_u32(sQ) + kk * 2048, TILE_BYTES, 1024);
+      umma_f16(tmem + 256, aP, bDO, id_mm, kk != 0);    // dV[k,d] += P_drop^T dO
+      umma_f16(tmem + 320, aDS, bQ, id_mm, kk != 0);    // dK[k,d] += dS^T Q
+      // reduction over keys: dS K-major (two 64-wide regions), K tile MN-major
+      const uint64_t aDSk = umma_desc_sw128(smem_u32(sDS) + (kk >> 2) * TILE_BYTES + (kk & 3) * 32, 16, 1024);
+      const uint64_t bK = umma_desc_sw128(smem_u32(sK) + kk * 2048, TILE_BYTES, 1024);
+      umma_f16(tmem + 384, aDSk, bK, id_km, kk != 0);   // dQ[q,d] += dS K
+    }
+    umma_commit(&bars[2]);
+  }
+  mbar_wait(&bars[2], 0);
+  __syncwarp();
+  tc_fence_after();
+  {
+    T* base = reinterpret_cast<T*>(P.out) + static_cast<size_t>(row0 + tid) * (3 * P.H) + h * AT_D;
+#pragma unroll
+    for (int which = 0; which < 3; ++which) {
+      // which: 0 -> dQ (TMEM 384), 1 -> dK (320), 2 -> dV (256)
+      const uint32_t col = which == 0 ? 384u : (which == 1 ? 320u : 256u);
+      T* dst = base + which * P.H;
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(t_row + col + c * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          uint4 u;
+          u.x = Cvt<T>::pack2(__uint_as_float(r[i * 8 + 0]), __uint_as_float(r[i * 8 + 1]));
+          u.y = Cvt<T>::pack2(__uint_as_float(r[i * 8 + 2]), __uint_as_float(r[i * 8 + 3]));
+          u.z = Cvt<T>::pack2(__uint_as_float(r[i * 8 + 4]), __uint_as_float(r[i * 8 + 5]));
+          u.w = Cvt<T>::pack2(__uint_as_float(r[i * 8 + 6]), __uint_as_float(r[i * 8 + 7]));
+          reinterpret_cast<uint4*>(dst + c * 32)[i] = u;
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc(tmem, 512);
+  }
+}
+
+constexpr int ATTN_FWD_SMEM = 3 * TILE_BYTES + PBUF_BYTES + AT_S * 4 + 64 + 1024;
+constexpr int ATTN_BWD_SMEM = 4 * TILE_BYTES + 2 * PBUF_BYTES + AT_S * 4 + 64 + 1024;
+
+static int attn_check(const char* who, int B, int S, int heads, int H) {
+  if (S != AT_S || heads <= 0 || H != heads * AT_D || B <= 0) {
+    set_last_error("%s: unsupported shape B=%d S=%d heads=%d H=%d (needs S=%d, head_dim=%d)", who, B, S, heads, H, AT_S, AT_D);
+    return 1;
+  }
+  return 0;
+}
+
+}  // namespace hs
+
+using namespace hs;
+
+extern "C" int hs_attention_supported(int S, int head_dim) { return (S == AT_S && head_dim == AT_D) ? 1 : 0; }
+
+extern "C" int hs_attention_fwd(const void* qkv, const float* mask, void* ctx, float* lse, int B, int S, int heads,
+                                int H, float dropout_p, const long long* seed, unsigned site, int dtype,
+                                hs_stream_t stream) {
+  if (attn_check("hs_attention_fwd", B, S, heads, H)) return 1;
+  if (dropout_p > 0.f && seed == nullptr) { set_last_error("hs_attention_fwd: dropout needs a seed pointer"); return 1; }
+  CUtensorMap tm;
+  if (make_tmap_2d_16b(&tm, qkv, 3ull * H, static_cast<uint64_t>(B) * S, 3ull * H, 64, AT_S)) return 1;
+  AttnParams P{mask, ctx, nullptr, nullptr, lse, B, heads, H, 0.125f, dropout_p, seed, site};
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int grid = B * heads;
+  if (dtype == HS_F16) {
+    static bool done = false;
+    if (!done) { HS_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATTN_FWD_SMEM)); done = true; }
+    attn_fwd_kernel<__half><<<grid, AT_THREADS, ATTN_FWD_SMEM, s>>>(tm, P);
+  } else if (dtype == HS_BF16) {
+    static bool done = false;
+    if (!done) { HS_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATTN_FWD_SMEM)); done = true; }
+    attn_fwd_kernel<__nv_bfloat16><<<grid, AT_THREADS, ATTN_FWD_SMEM, s>>>(tm, P);
+  } else { set_last_error("hs_attention_fwd: dtype must be f16 or bf16"); return 1; }
+  return post_launch("attn_fwd_kernel");
+}
+
+extern "C" int hs_attention_bwd(const void* qkv, const float* mask, const void* ctx, const void* dctx, const float* lse,
+                                void* dqkv, int B, int S, int heads, int H, float dropout_p, const long long* seed,
+                                unsigned site, int dtype, hs_stream_t stream) {
+  if (attn_check("hs_attention_bwd", B, S, heads, H)) return 1;
+  if (dropout_p > 0.f && seed == nullptr) { set_last_error("hs_attention_bwd: dropout needs a seed pointer"); return 1; }
+  CUtensorMap tmQ, tmD;
+  if (make_tmap_2d_16b(&tmQ, qkv, 3ull * H, static_cast<uint64_t>(B) * S, 3ull * H, 64, AT_S)) return 1;
+  if (make_tmap_2d_16b(&tmD, dctx, static_cast<uint64_t>(H), static_cast<uint64_t>(B) * S, static_cast<uint64_t>(H), 64, AT_S)) return 1;
+  AttnParams P{mask, dqkv, ctx, dctx, const_cast<float*>(lse), B, heads, H, 0.125f, dropout_p, seed, site};
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int grid = B * heads;
+  if (dtype == HS_F16) {
+    static bool done = false;
+    if (!done) { HS_CUDA_OK(cudaFuncSetAttribute(attn_bwd_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATTN_BWD_SMEM)); done = true; }
+    attn_bwd_kernel<__half><<<grid, AT_THREADS, ATTN_BWD_SMEM, s>>>(tmQ, tmD, P);
+  } else if (dtype == HS_BF16) {
+    static bool done = false;
+    if (!done) { HS_CUDA_OK(cudaFuncSetAttribute(attn_bwd_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATTN_BWD_SMEM)); done = true; }
+    attn_bwd_kernel<__nv_bfloat16><<<grid, AT_THREADS, ATTN_BWD_SMEM, s>>>(tmQ, tmD, P);
+  } else { set_last_error("hs_attention_bwd: dtype must be f16 or bf16"); return 1; }
+  return post_launch("attn_bwd_kernel");
+}

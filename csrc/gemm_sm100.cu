@@ -319,6 +319,14 @@ static PFN_encodeTiled get_encode_fn() {
 
 int make_tmap_2d_16b(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t ld,
                      uint32_t box_inner, uint32_t box_outer) {
+  // cuTensorMapEncodeTiled is a driver-API call: it needs the primary context to be current on THIS
+  // thread. A thread that has only ever inherited the default device (e.g. PyTorch's autograd worker
+  // on device 0) has no context bound until its first context-requiring runtime call -- force that.
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) {
+    (void)cudaFree(nullptr);
+    ctx_bound = true;
+  }
   PFN_encodeTiled enc = get_encode_fn();
   if (enc == nullptr) {
     set_last_error("cuTensorMapEncodeTiled is not available from the CUDA driver");

@@ -85,7 +85,13 @@ def build_cuda(force: bool = False, verbose: bool = False) -> Path:
 
     with cf.ThreadPoolExecutor(max_workers=min(8, max(1, len(srcs)))) as ex:
         objs = list(ex.map(compile_one, srcs))
-    _run([nvcc, "-shared", "-o", str(CUDA_LIB), *map(str, objs), "-cudart", "static"])
+    # Shared cudart on purpose: the library must see the same per-thread current device / primary
+    # context as the host program (PyTorch's autograd threads call into it), which a private static
+    # runtime would not. libcudart.so.12 resolves to the copy already loaded by torch; the rpath is the
+    # fallback for stand-alone C/C++ hosts.
+    cuda_lib_dir = str(Path(nvcc).resolve().parents[1] / "lib64")
+    _run([nvcc, "-shared", "-o", str(CUDA_LIB), *map(str, objs), "-cudart", "shared",
+          "-Xlinker", "-rpath", "-Xlinker", cuda_lib_dir])
     stamp.write_text(want)
     return CUDA_LIB
 

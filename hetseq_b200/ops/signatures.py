@@ -17,5 +17,7 @@ SIGNATURES = {
     'hs_embed_scatter_word': [vp, vp, ci, vp, ci, ci, ci, ci, vp],
     'hs_sum_over_batch': [vp, ci, cl, vp, ci, ci, vp],
     'hs_colsum_rows_where': [vp, vp, ci, cl, ci, ci, vp, ci, vp, ci, vp],
+    'hs_attention_fwd': [vp, vp, vp, vp, ci, ci, ci, ci, cf, vp, cu, ci, vp],
+    'hs_attention_bwd': [vp, vp, vp, vp, vp, vp, ci, ci, ci, ci, cf, vp, cu, ci, vp],
     'hs_adadelta_flat': [vp, vp, vp, vp, vp, ci, cl, ci, cl, cf, cf, cf, cf, cf, vp, vp, vp, vp],
 }

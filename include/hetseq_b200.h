@@ -143,6 +143,20 @@ HS_API int hs_sum_over_batch(const void* x, int B, long long inner, float* out, 
 HS_API int hs_colsum_rows_where(const void* x, const void* sel, int sel_i64, long long want, int M, int N, float* out,
                                 int accumulate, float* scratch, int dtype, hs_stream_t stream);
 
+/* ---- fused attention on tcgen05 (csrc/attention_sm100.cu; bert_modeling.py:351-377, K2-K4/W4) -------- */
+/* 1 when the fused kernel handles this (sequence length, head dim); callers must check first. */
+HS_API int hs_attention_supported(int S, int head_dim);
+/* ctx[M,H] = merge_heads(dropout(softmax(Q K^T / sqrt(d) + mask)) V) from the packed projection
+ * qkv [M, 3H] (q | k | v column blocks, heads of 64 inside each). mask: [B,S] additive fp32.
+ * lse: [B*heads*S] log-sum-exp of the scaled+masked scores (kept for backward). */
+HS_API int hs_attention_fwd(const void* qkv, const float* mask, void* ctx, float* lse, int B, int S, int heads,
+                            int H, float dropout_p, const long long* seed, unsigned site, int dtype,
+                            hs_stream_t stream);
+/* dqkv [M, 3H] from dctx [M,H]; recomputes the probabilities and the dropout mask. */
+HS_API int hs_attention_bwd(const void* qkv, const float* mask, const void* ctx, const void* dctx, const float* lse,
+                            void* dqkv, int B, int S, int heads, int H, float dropout_p, const long long* seed,
+                            unsigned site, int dtype, hs_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -37,7 +37,7 @@ def _build(tmp_path, dtype_flag, kernels, seed=0, **cfgkw):
     return ctl, task
 
 
-def _batch(vocab=2000, B=8, S=64):
+def _batch(vocab=2000, B=8, S=128):
     from hetseq_b200.data.bert_dataset import SyntheticBertData
     return SyntheticBertData(B, S, 10, vocab, seed=3).fetch_rows(list(range(B)))
 
@@ -61,14 +61,16 @@ def test_native_loss_and_grads_match_torch(tmp_path, flag):
     ref_loss.backward()
     assert abs(loss.item() - ref_loss.item()) < (0.05 if flag == '--bf16' else 0.02), (loss.item(), ref_loss.item())
     named = dict(ref.named_parameters())
-    worst = 0.0
+    errs = {}
     for name, p in ctl.get_model().named_parameters():
         g, rg = p.main_grad.float(), named[name].grad
-        denom = rg.abs().max().item() + 1e-6
-        err = (g - rg).abs().max().item() / denom
-        worst = max(worst, err)
-        assert err < (0.12 if flag == '--bf16' else 0.04), (name, err)
-    print('worst relative grad error', worst)
+        # relative error in the Frobenius norm: 16-bit activations vs the fp32 oracle
+        if 'key.bias' in name:
+            continue   # mathematically zero (softmax is shift invariant per row): only noise to compare
+        errs[name] = ((g - rg).norm() / (rg.norm() + 1e-12)).item()
+    top = sorted(errs.items(), key=lambda kv: -kv[1])[:8]
+    print('largest relative gradient errors:', top)
+    assert top[0][1] < (0.15 if flag == '--bf16' else 0.10), top
 
 
 def test_native_training_reduces_loss(tmp_path):
