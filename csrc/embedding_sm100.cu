@@ -164,7 +164,7 @@ extern "C" int hs_sum_over_batch(const void* x, int B, long long inner, float* o
 extern "C" int hs_colsum_rows_where(const void* x, const void* sel, int sel_i64, long long want, int M, int N, float* out,
                                     int accumulate, float* scratch, int dtype, hs_stream_t stream) {
   if (M <= 0 || N <= 0 || N % 8 != 0 || scratch == nullptr) { set_last_error("hs_colsum_rows_where: bad arguments"); return 1; }
-  const int slabs = (M + 63) / 64 < 64 ? (M + 63) / 64 : 64;
+  const int slabs = colsum_slabs(M);
   const int rows_per_block = (M + slabs - 1) / slabs;
   dim3 grid((N / 8 + 255) / 256, slabs);
   cudaStream_t s = static_cast<cudaStream_t>(stream);

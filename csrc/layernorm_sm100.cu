@@ -134,7 +134,7 @@ struct LnBwdParams {
   const void* dy; const void* z; const void* gamma; const float* mean; const float* rstd;
   void* dz;       // gradient w.r.t. z (the residual path), 16-bit
   void* dx;       // gradient w.r.t. x = dz * dropout mask (NULL when p == 0 and dz suffices)
-  float* part_dgamma; float* part_dbeta;   // [gridDim.x, H] partial sums (scratch)
+  float* dgamma; float* dbeta;             // fp32 destinations, accumulated with one atomicAdd per block and column
   int M, H; float p; const long long* seed; uint32_t site;
   int post_dropout;  // 1: dy is first multiplied by the mask (embeddings: y = dropout(LN(z)))
   int rows_per_block;
@@ -231,40 +231,41 @@ __global__ void __launch_bounds__(LN_THREADS) ln_bwd_kernel(LnBwdParams P) {
       a += sm[static_cast<size_t>(w) * 2 * P.H + i];
       b += sm[static_cast<size_t>(w) * 2 * P.H + P.H + i];
     }
-    P.part_dgamma[static_cast<size_t>(blockIdx.x) * P.H + i] = a;
-    P.part_dbeta[static_cast<size_t>(blockIdx.x) * P.H + i] = b;
+    if (P.dgamma) atomicAdd(P.dgamma + i, a);
+    if (P.dbeta) atomicAdd(P.dbeta + i, b);
   }
 }
 
-// out[h] (= or +=) sum over parts of part[part, h]; fp32 output (the flat main-grad buffer)
-__global__ void __launch_bounds__(256)
-colsum_parts_kernel(const float* __restrict__ part, int nparts, int H, float* __restrict__ out, int accumulate) {
-  const int h = blockIdx.x * blockDim.x + threadIdx.x;
-  if (h >= H) return;
-  float a = 0.f;
-  for (int i = 0; i < nparts; ++i) a += part[static_cast<size_t>(i) * H + h];
-  out[h] = accumulate ? out[h] + a : a;
-}
-
-// Column sums of a 16-bit [M, N] matrix (bias gradients): stage 1 partials over row slabs.
+// Column sums of a 16-bit [M, N] matrix (bias gradients): block = 32 lanes x 8 rows, each lane owns 8
+// consecutive columns (256 columns per block), rows strided by 8 inside a slab of rows; the block's 256
+// column sums are reduced in shared memory and added to the fp32 destination with one atomicAdd each.
 template <typename T>
 __global__ void __launch_bounds__(256)
 colsum_partial_kernel(const T* __restrict__ x, int M, int N, int ld, int rows_per_block, float* __restrict__ part) {
-  // each thread owns 8 consecutive columns
-  const int c8 = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c8 * 8 >= N) return;
+  __shared__ float red[8][32][9];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c0 = (blockIdx.x * 32 + tx) * 8;
   const int r0 = blockIdx.y * rows_per_block, r1 = min(M, r0 + rows_per_block);
   float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  for (int r = r0; r < r1; ++r) {
-    float f[8];
-    unpack8<T>(*reinterpret_cast<const uint4*>(x + static_cast<size_t>(r) * ld + c8 * 8), f);
+  if (c0 < N) {
+    for (int r = r0 + ty; r < r1; r += 8) {
+      float f[8];
+      unpack8<T>(*reinterpret_cast<const uint4*>(x + static_cast<size_t>(r) * ld + c0), f);
 #pragma unroll
-    for (int k = 0; k < 8; ++k) acc[k] += f[k];
+      for (int k = 0; k < 8; ++k) acc[k] += f[k];
+    }
   }
-  float* dst = part + static_cast<size_t>(blockIdx.y) * N + c8 * 8;
 #pragma unroll
-  for (int k = 0; k < 8; ++k)
-    if (c8 * 8 + k < N) dst[k] = acc[k];
+  for (int k = 0; k < 8; ++k) red[ty][tx][k] = acc[k];
+  __syncthreads();
+  // 256 threads -> 256 columns of this block
+  const int col = threadIdx.x;          // 0..255
+  const int lx = col >> 3, lk = col & 7;
+  float t = 0.f;
+#pragma unroll
+  for (int y = 0; y < 8; ++y) t += red[y][lx][lk];
+  const int c = blockIdx.x * 256 + col;
+  if (c < N) atomicAdd(part + c, t);
 }
 
 static int ln_check(const char* who, int M, int H) {
@@ -302,27 +303,21 @@ extern "C" int hs_ln_fwd(const void* x, const void* bias, const void* residual, 
   return post_launch("ln_fwd_kernel");
 }
 
-extern "C" int hs_ln_bwd_scratch_elems(int M, int H) {
-  const int blocks = num_sms() * 4;
-  const int rpb = (M + blocks - 1) / blocks;
-  const int rows_per_block = ((rpb + LN_ROWS_PER_BLOCK - 1) / LN_ROWS_PER_BLOCK) * LN_ROWS_PER_BLOCK;
-  const int grid = (M + rows_per_block - 1) / rows_per_block;
-  return 2 * grid * H;
-}
-
 extern "C" int hs_ln_bwd(const void* dy, const void* z, const void* gamma, const float* mean, const float* rstd,
-                         void* dz, void* dx, float* dgamma, float* dbeta, int accumulate_params, float* scratch,
+                         void* dz, void* dx, float* dgamma, float* dbeta, int accumulate_params,
                          int M, int H, float dropout_p, const long long* seed, unsigned site, int post_dropout,
                          int dtype, hs_stream_t stream) {
   if (ln_check("hs_ln_bwd", M, H)) return 1;
-  if (scratch == nullptr) { set_last_error("hs_ln_bwd: scratch is required"); return 1; }
-  const int blocks = num_sms() * 4;
+  const int blocks = num_sms() * 2;
   const int rpb = (M + blocks - 1) / blocks;
   const int rows_per_block = ((rpb + LN_ROWS_PER_BLOCK - 1) / LN_ROWS_PER_BLOCK) * LN_ROWS_PER_BLOCK;
   const int grid = (M + rows_per_block - 1) / rows_per_block;
-  float* part_g = scratch;
-  float* part_b = scratch + static_cast<size_t>(grid) * H;
-  LnBwdParams P{dy, z, gamma, mean, rstd, dz, dx, part_g, part_b, M, H, dropout_p, seed, site, post_dropout, rows_per_block};
+  cudaStream_t s0 = static_cast<cudaStream_t>(stream);
+  if (!accumulate_params) {   // overwrite semantics: clear the destinations, then accumulate into them
+    if (dgamma) HS_CUDA_OK(cudaMemsetAsync(dgamma, 0, sizeof(float) * H, s0));
+    if (dbeta) HS_CUDA_OK(cudaMemsetAsync(dbeta, 0, sizeof(float) * H, s0));
+  }
+  LnBwdParams P{dy, z, gamma, mean, rstd, dz, dx, dgamma, dbeta, M, H, dropout_p, seed, site, post_dropout, rows_per_block};
   const size_t smem = static_cast<size_t>(LN_ROWS_PER_BLOCK) * 2 * H * sizeof(float);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (smem > 48 * 1024) { set_last_error("hs_ln_bwd: H=%d needs %zu B of shared memory", H, smem); return 1; }
@@ -338,37 +333,31 @@ extern "C" int hs_ln_bwd(const void* dy, const void* z, const void* gamma, const
   else if (dtype == HS_BF16) HS_LN_BWD(__nv_bfloat16);
   else { set_last_error("hs_ln_bwd: dtype must be f16 or bf16"); return 1; }
 #undef HS_LN_BWD
-  if (post_launch("ln_bwd_kernel")) return 1;
-  if (dgamma) {
-    colsum_parts_kernel<<<(H + 255) / 256, 256, 0, s>>>(part_g, grid, H, dgamma, accumulate_params);
-    if (post_launch("colsum_parts_kernel")) return 1;
-  }
-  if (dbeta) {
-    colsum_parts_kernel<<<(H + 255) / 256, 256, 0, s>>>(part_b, grid, H, dbeta, accumulate_params);
-    if (post_launch("colsum_parts_kernel")) return 1;
-  }
-  return 0;
+  return post_launch("ln_bwd_kernel");
 }
 
-extern "C" int hs_colsum_scratch_elems(int M, int N) {
-  const int slabs = (M + 63) / 64 < 64 ? (M + 63) / 64 : 64;
-  return slabs * N;
+namespace hs {
+int colsum_slabs(int M) {
+  const int s = (M + 127) / 128;
+  return s < 1 ? 1 : (s > 128 ? 128 : s);
 }
+}  // namespace hs
 
-extern "C" int hs_colsum(const void* x, int M, int N, int ld, float* out, int accumulate, float* scratch, int dtype,
+extern "C" int hs_colsum_scratch_elems(int M, int N) { return colsum_slabs(M) * N; }
+
+extern "C" int hs_colsum(const void* x, int M, int N, int ld, float* out, int accumulate, int dtype,
                          hs_stream_t stream) {
-  if (M <= 0 || N <= 0 || ld % 8 != 0 || scratch == nullptr) {
-    set_last_error("hs_colsum: bad arguments M=%d N=%d ld=%d scratch=%p", M, N, ld, (void*)scratch);
+  if (M <= 0 || N <= 0 || ld % 8 != 0) {
+    set_last_error("hs_colsum: bad arguments M=%d N=%d ld=%d", M, N, ld);
     return 1;
   }
-  const int slabs = (M + 63) / 64 < 64 ? (M + 63) / 64 : 64;
+  const int slabs = colsum_slabs(M);
   const int rows_per_block = (M + slabs - 1) / slabs;
-  dim3 grid(((N + 7) / 8 + 255) / 256, slabs);
+  dim3 grid((N + 255) / 256, slabs);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  if (dtype == HS_F16) colsum_partial_kernel<__half><<<grid, 256, 0, s>>>((const __half*)x, M, N, ld, rows_per_block, scratch);
-  else if (dtype == HS_BF16) colsum_partial_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>((const __nv_bfloat16*)x, M, N, ld, rows_per_block, scratch);
+  if (!accumulate) HS_CUDA_OK(cudaMemsetAsync(out, 0, sizeof(float) * N, s));
+  if (dtype == HS_F16) colsum_partial_kernel<__half><<<grid, 256, 0, s>>>((const __half*)x, M, N, ld, rows_per_block, out);
+  else if (dtype == HS_BF16) colsum_partial_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>((const __nv_bfloat16*)x, M, N, ld, rows_per_block, out);
   else { set_last_error("hs_colsum: dtype must be f16 or bf16"); return 1; }
-  if (post_launch("colsum_partial_kernel")) return 1;
-  colsum_parts_kernel<<<(N + 255) / 256, 256, 0, s>>>(scratch, slabs, N, out, accumulate);
-  return post_launch("colsum_parts_kernel");
+  return post_launch("colsum_partial_kernel");
 }

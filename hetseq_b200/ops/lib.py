@@ -60,7 +60,6 @@ def load() -> ctypes.CDLL:
     lib.hs_launch_count.restype = ctypes.c_uint64
     for fn in ('hs_sumsq_scratch_elems',):
         getattr(lib, fn).restype = ctypes.c_int
-    lib.hs_ln_bwd_scratch_elems.argtypes = [ctypes.c_int, ctypes.c_int]
     lib.hs_colsum_scratch_elems.argtypes = [ctypes.c_int, ctypes.c_int]
     lib.hs_attention_supported.argtypes = [ctypes.c_int, ctypes.c_int]
     _declare(lib)

@@ -73,18 +73,16 @@ def ln_bwd(dy, z, gamma, mean, rstd, dgamma, dbeta, accumulate_params, *, p=0.0,
     M, H = dy.shape
     dz = torch.empty_like(dy)
     dx = torch.empty_like(dy) if (need_dx and p > 0.0 and not post_dropout) else None
-    sc = scratch(dy.device, int(L.hs_ln_bwd_scratch_elems(M, H)), 'ln_bwd')
     lib.check(L.hs_ln_bwd(dy.data_ptr(), z.data_ptr(), gamma.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
                           dz.data_ptr(), lib.ptr(dx), lib.ptr(dgamma), lib.ptr(dbeta), int(accumulate_params),
-                          sc.data_ptr(), M, H, float(p), lib.ptr(seed), int(site), int(post_dropout),
+                          M, H, float(p), lib.ptr(seed), int(site), int(post_dropout),
                           lib.dtype_code(dy.dtype), lib.stream_ptr()), 'hs_ln_bwd')
     return dz, (dx if dx is not None else dz)
 
 
 def colsum(x, M, N, ld, out, accumulate):
     L = lib.load()
-    sc = scratch(x.device, int(L.hs_colsum_scratch_elems(M, N)), 'colsum')
-    lib.check(L.hs_colsum(x.data_ptr(), M, N, ld, out.data_ptr(), int(accumulate), sc.data_ptr(),
+    lib.check(L.hs_colsum(x.data_ptr(), M, N, ld, out.data_ptr(), int(accumulate),
                           lib.dtype_code(x.dtype), lib.stream_ptr()), 'hs_colsum')
     return out
 

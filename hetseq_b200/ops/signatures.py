@@ -8,8 +8,8 @@ SIGNATURES = {
     'hs_sumsq': [vp, ci, cl, ci, cl, vp, vp, ci, vp],
     'hs_adam_flat': [vp, vp, vp, vp, vp, ci, cl, ci, cl, cf, cf, cf, cf, cf, cf, cf, vp, vp, vp, vp],
     'hs_ln_fwd': [vp, vp, vp, vp, vp, vp, vp, vp, vp, ci, ci, cf, cf, vp, cu, ci, ci, vp],
-    'hs_ln_bwd': [vp, vp, vp, vp, vp, vp, vp, vp, vp, ci, vp, ci, ci, cf, vp, cu, ci, ci, vp],
-    'hs_colsum': [vp, ci, ci, ci, vp, ci, vp, ci, vp],
+    'hs_ln_bwd': [vp, vp, vp, vp, vp, vp, vp, vp, vp, ci, ci, ci, cf, vp, cu, ci, ci, vp],
+    'hs_colsum': [vp, ci, ci, ci, vp, ci, ci, vp],
     'hs_xent': [vp, ci, vp, ci, ci, ci, vp, vp, ci, ci, ci, vp],
     'hs_gather_rows': [vp, vp, ci, vp, ci, ci, vp],
     'hs_scatter_add_rows': [vp, vp, ci, vp, ci, ci, ci, vp],

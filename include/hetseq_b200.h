@@ -106,17 +106,18 @@ HS_API int hs_adadelta_flat(const float* grad, float* master, float* square_avg,
 HS_API int hs_ln_fwd(const void* x, const void* bias, const void* residual, const void* gamma, const void* beta,
                      void* y, void* z, float* mean, float* rstd, int M, int H, float eps, float dropout_p,
                      const long long* seed, unsigned site, int post_dropout, int dtype, hs_stream_t stream);
-HS_API int hs_ln_bwd_scratch_elems(int M, int H);
 /* dz = dLN/dz (residual path), dx = dz * dropout mask (GEMM path, may be NULL), dgamma/dbeta fp32
- * (= or += per accumulate_params) via per-block partials in `scratch` + a deterministic second stage. */
+ * (= or += per accumulate_params): per-block partial sums in registers/shared memory, then one
+ * atomicAdd per block and column straight into the destination (the flat main-grad buffer). */
 HS_API int hs_ln_bwd(const void* dy, const void* z, const void* gamma, const float* mean, const float* rstd,
-                     void* dz, void* dx, float* dgamma, float* dbeta, int accumulate_params, float* scratch,
+                     void* dz, void* dx, float* dgamma, float* dbeta, int accumulate_params,
                      int M, int H, float dropout_p, const long long* seed, unsigned site, int post_dropout,
                      int dtype, hs_stream_t stream);
-HS_API int hs_colsum_scratch_elems(int M, int N);
 /* out[n] (= or +=) sum_m x[m,n] for a 16-bit [M,N] matrix: the bias gradients of every Linear. */
-HS_API int hs_colsum(const void* x, int M, int N, int ld, float* out, int accumulate, float* scratch, int dtype,
+HS_API int hs_colsum(const void* x, int M, int N, int ld, float* out, int accumulate, int dtype,
                      hs_stream_t stream);
+/* Floats of scratch needed by hs_colsum_rows_where (row-slab partial sums). */
+HS_API int hs_colsum_scratch_elems(int M, int N);
 
 /* ---- fused cross-entropy + MLM row gather/scatter (csrc/xent_sm100.cu) ------------------------------- */
 /* CrossEntropyLoss(ignore_index=-1), mean reduction (bert_modeling.py:881-886, K13). Per row: online
