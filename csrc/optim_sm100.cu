@@ -15,6 +15,8 @@
 #include "host.h"
 #include "../include/hetseq_b200.h"
 
+#include <mutex>
+
 namespace hs {
 
 constexpr int OPT_THREADS = 256;
@@ -200,6 +202,62 @@ extern "C" int hs_sumsq(const void* grad, int dtype, long long nchunks, int chun
   else if (dtype == HS_F16) sumsq_partial_kernel<__half><<<grid, OPT_THREADS, 0, s>>>((const __half*)grad, nchunks, chunk, stride, scratch);
   else if (dtype == HS_BF16) sumsq_partial_kernel<__nv_bfloat16><<<grid, OPT_THREADS, 0, s>>>((const __nv_bfloat16*)grad, nchunks, chunk, stride, scratch);
   else { set_last_error("hs_sumsq: bad dtype %d", dtype); return 1; }
+  if (post_launch("sumsq_partial_kernel")) return 1;
+  sumsq_final_kernel<<<1, OPT_THREADS, 0, s>>>(scratch, grid, out, accumulate);
+  return post_launch("sumsq_final_kernel");
+}
+
+// ---- allocation-free variant of hs_sumsq ----------------------------------------------------------
+// Some hosts of this library cannot hand it a scratch buffer: a process that has given the whole GPU
+// to its own memory pool up front (any later cudaMalloc may fail, and cudaMalloc/cudaFree synchronise
+// the device, which a latency-critical step loop cannot afford), or a plain C/C++ program that links
+// the C ABI and has no caching allocator to borrow from. For them the block partials live in a small
+// array that is part of the library image itself. Every GPU that loads the library holds these 16 KiB
+// until the process exits.
+constexpr int HS_SUMSQ_NOALLOC_MAX_PARTIALS = 4096;
+static __device__ __align__(256) float g_sumsq_static_scratch[HS_SUMSQ_NOALLOC_MAX_PARTIALS];
+
+namespace hs {
+// In host code the symbol above is only a handle; the device address has to be looked up, once per
+// device and with that device current.
+static int sumsq_static_scratch(float** out) {
+  static float* ptr_by_device[64] = {nullptr};
+  static std::mutex mu;
+  int dev = 0;
+  HS_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) { set_last_error("hs_sumsq_noalloc: device index %d is out of range", dev); return 1; }
+  std::lock_guard<std::mutex> lock(mu);
+  if (ptr_by_device[dev] == nullptr) {
+    float* p = nullptr;
+    HS_CUDA_OK(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_sumsq_static_scratch));
+    ptr_by_device[dev] = p;
+  }
+  *out = ptr_by_device[dev];
+  return 0;
+}
+}  // namespace hs
+
+extern "C" int hs_sumsq_noalloc_max_partials(void) { return HS_SUMSQ_NOALLOC_MAX_PARTIALS; }
+
+extern "C" int hs_sumsq_noalloc(const void* grad, int dtype, long long nchunks, int chunk, long long stride,
+                                float* out, int accumulate, hs_stream_t stream) {
+  if (check_layout("hs_sumsq_noalloc", nchunks, chunk, stride)) return 1;
+  if (out == nullptr) { set_last_error("hs_sumsq_noalloc: out is required"); return 1; }
+  const int grid = opt_grid(nchunks);
+  if (grid > HS_SUMSQ_NOALLOC_MAX_PARTIALS) {
+    set_last_error("hs_sumsq_noalloc: this launch needs %d block partials but the built-in scratch holds %d; "
+                   "use hs_sumsq with caller-provided scratch", grid, HS_SUMSQ_NOALLOC_MAX_PARTIALS);
+    return 1;
+  }
+  float* scratch = nullptr;
+  if (sumsq_static_scratch(&scratch)) return 1;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  // Stage 1 overwrites partials [0, grid) and stage 2 reads exactly those, so nothing left behind by an
+  // earlier call is ever consumed and nothing needs clearing first.
+  if (dtype == HS_F32) sumsq_partial_kernel<float><<<grid, OPT_THREADS, 0, s>>>((const float*)grad, nchunks, chunk, stride, scratch);
+  else if (dtype == HS_F16) sumsq_partial_kernel<__half><<<grid, OPT_THREADS, 0, s>>>((const __half*)grad, nchunks, chunk, stride, scratch);
+  else if (dtype == HS_BF16) sumsq_partial_kernel<__nv_bfloat16><<<grid, OPT_THREADS, 0, s>>>((const __nv_bfloat16*)grad, nchunks, chunk, stride, scratch);
+  else { set_last_error("hs_sumsq_noalloc: bad dtype %d", dtype); return 1; }
   if (post_launch("sumsq_partial_kernel")) return 1;
   sumsq_final_kernel<<<1, OPT_THREADS, 0, s>>>(scratch, grid, out, accumulate);
   return post_launch("sumsq_final_kernel");

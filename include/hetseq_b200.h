@@ -81,6 +81,23 @@ HS_API int hs_sumsq_scratch_elems(void);
  * partials into `scratch`, then one block reduces them. Replaces the norm loop of optim.py:65-70. */
 HS_API int hs_sumsq(const void* grad, int dtype, long long nchunks, int chunk, long long stride,
                     float* scratch, float* out, int accumulate, hs_stream_t stream);
+/* Same result as hs_sumsq for callers that cannot allocate device memory, so cannot supply `scratch`:
+ * processes whose GPU memory is entirely pre-assigned to their own pool (a late cudaMalloc can fail, and
+ * cudaMalloc/cudaFree synchronise the device in the middle of a step loop), and bare C/C++ hosts of this
+ * ABI that have no caching allocator to draw from. The block partials go to an array built into the
+ * library: 4096 floats (16 KiB) per GPU, held from library load until process exit. The call makes no
+ * cudaMalloc/cudaFree and uses no allocating library routine. Limits and rules:
+ *   - it needs min(nchunks, 8 * SM count) partials; more than hs_sumsq_noalloc_max_partials() (4096)
+ *     is refused with an error -- use hs_sumsq then;
+ *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress, with
+ *     that device current); make that first call before starting any stream capture;
+ *   - all calls on a device share the one array. A call overwrites every partial it later reads, so
+ *     stale contents are harmless, but two calls that run concurrently on the GPU (different streams)
+ *     race on it: serialise them.
+ * No counterpart in the reference (it has no native code and never computes a flat gradient norm). */
+HS_API int hs_sumsq_noalloc(const void* grad, int dtype, long long nchunks, int chunk, long long stride,
+                            float* out, int accumulate, hs_stream_t stream);
+HS_API int hs_sumsq_noalloc_max_partials(void);
 /* fairseq Adam on flat memory, math of optim.py:162-231 (decoupled decay before the update, bias
  * correction via step_factor = sqrt(1-b2^t)/(1-b1^t), eps outside the sqrt). The gradient is read
  * once and multiplied by mult_host * (*mult_dev) on the fly -- this is where multiply_grads
