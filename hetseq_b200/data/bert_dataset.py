@@ -151,7 +151,8 @@ class SyntheticBertData(torch.utils.data.Dataset):
         for j, r in enumerate(rows):
             g = np.random.default_rng((self.seed, int(r)))
             length = int(g.integers(S // 2, S + 1))
-            ids[j] = g.integers(1000, self.vocab_size, size=S)
+            lo = min(1000, max(1, self.vocab_size // 10))   # skip the special-token range of real vocabularies
+            ids[j] = g.integers(lo, self.vocab_size, size=S)
             ids[j, length:] = 0
             mask[j, :length] = 1
             split = int(g.integers(1, max(2, length - 1)))
@@ -159,7 +160,7 @@ class SyntheticBertData(torch.utils.data.Dataset):
             k = int(min(P, max(1, round(0.15 * length))))
             p = np.sort(g.choice(np.arange(1, length), size=k, replace=False))
             pos[j, :k] = p
-            mids[j, :k] = g.integers(1000, self.vocab_size, size=k)
+            mids[j, :k] = g.integers(lo, self.vocab_size, size=k)
             nsp[j] = int(g.integers(0, 2))
         return ids, seg, mask, pos, mids, nsp
 

@@ -41,8 +41,10 @@ class NativeFlatUpdate(object):
                   'hs_sumsq')
         return self.sumsq_out[0].clone()
 
-    def update(self, mult) -> None:
+    def update(self, mult, skip=None) -> None:
+        """``skip``: 0-dim bool tensor; when true on the device the kernel leaves everything untouched."""
         opt, buf = self.opt, self.opt.buffer
+        skip_i = None if skip is None else skip.to(torch.int32).reshape(1)
         h = opt.hyper
         mult_dev = None
         mult_host = 1.0
@@ -61,14 +63,14 @@ class NativeFlatUpdate(object):
                 *args_common, opt.state['exp_avg'].data_ptr(), opt.state['exp_avg_sq'].data_ptr(),
                 self._base(buf.flat_param), out_dtype, self.nchunks, CHUNK, self.stride,
                 float(h['lr']), float(b1), float(b2), float(h['eps']), float(h['weight_decay']), float(step_factor),
-                mult_host, lib.ptr(mult_dev), None, None, lib.stream_ptr())
+                mult_host, lib.ptr(mult_dev), None, lib.ptr(skip_i), lib.stream_ptr())
             lib.check(rc, 'hs_adam_flat')
         else:
             rc = self.lib.hs_adadelta_flat(
                 *args_common, opt.state['square_avg'].data_ptr(), opt.state['acc_delta'].data_ptr(),
                 self._base(buf.flat_param), out_dtype, self.nchunks, CHUNK, self.stride,
                 float(h['lr']), float(h['rho']), float(h['eps']), float(h['weight_decay']),
-                mult_host, lib.ptr(mult_dev), None, None, lib.stream_ptr())
+                mult_host, lib.ptr(mult_dev), None, lib.ptr(skip_i), lib.stream_ptr())
             lib.check(rc, 'hs_adadelta_flat')
         if opt.sharded:
             opt.dp.all_gather_params(buf)

@@ -3,6 +3,7 @@ besides hs_gemm. Kept in one table so a stale library is detected at load time."
 import ctypes
 
 vp, ci, cf, cl, cu = ctypes.c_void_p, ctypes.c_int, ctypes.c_float, ctypes.c_longlong, ctypes.c_uint
+csz = ctypes.c_size_t
 
 SIGNATURES = {
     'hs_sumsq': [vp, ci, cl, ci, cl, vp, vp, ci, vp],
@@ -19,5 +20,14 @@ SIGNATURES = {
     'hs_colsum_rows_where': [vp, vp, ci, cl, ci, ci, vp, ci, vp, ci, vp],
     'hs_attention_fwd': [vp, vp, vp, vp, ci, ci, ci, ci, cf, vp, cu, ci, vp],
     'hs_attention_bwd': [vp, vp, vp, vp, vp, vp, ci, ci, ci, ci, cf, vp, cu, ci, vp],
+    'hs_ipc_alloc': [csz, ctypes.POINTER(vp), ctypes.c_char_p],
+    'hs_ipc_open': [ctypes.c_char_p, ctypes.POINTER(vp)],
+    'hs_ipc_close': [vp],
+    'hs_ipc_free': [vp],
+    'hs_dp_reduce_scatter': [vp, vp, ci, ci, cl, cl, ci, ci, cu, vp, ci, vp],
+    'hs_dp_norm_exchange': [vp, ci, ci, cu, vp, cf, vp, cf, vp, vp, vp],
+    'hs_dp_adam_allgather': [vp, vp, vp, vp, vp, vp, ci, ci, cl, ci, ci, cf, cf, cf, cf, cf, cf, vp, vp, cu, vp, ci, vp],
+    'hs_dp_wait_params': [vp, ci, ci, cu, vp],
+    'hs_sumsq_noalloc': [vp, ci, cl, ci, cl, vp, ci, vp],
     'hs_adadelta_flat': [vp, vp, vp, vp, vp, ci, cl, ci, cl, cf, cf, cf, cf, cf, vp, vp, vp, vp],
 }

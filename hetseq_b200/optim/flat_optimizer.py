@@ -177,6 +177,13 @@ class _Optimizer(object):
         """Global L2 norm of the (multiplied, unscaled) gradients; folds the clip coefficient into
         the pending multiplier. Mirrors optim.py:65-70 / torch.nn.utils.clip_grad_norm_
         (coef = max_norm / (norm + 1e-6), clamped to 1). Returns a 0-dim tensor; no host sync."""
+        if getattr(self.dp, 'fused', False):
+            # norm partials were accumulated by the reduce-scatter kernels; one exchange kernel gives
+            # every rank the same norm / clip coefficient / overflow flag
+            norm = self.dp.norm_exchange(self._mult / self._scale_used, self._mult_dev, float(max_norm))
+            self._skip = self.dp.scalars[2] != 0
+            self._fused_ready = True
+            return norm
         sumsq = self._local_sumsq()
         if self.sharded:
             sumsq = self.dp.all_reduce_scalar(sumsq)
@@ -192,31 +199,42 @@ class _Optimizer(object):
     def zero_grad(self):
         self.buffer.zero_grad()
         self._mult, self._mult_dev, self._skip = 1.0, None, None
+        self._fused_ready = False
 
     # -- update ---------------------------------------------------------------------------------
     def step(self, closure=None):
-        """One fused pass over the owned range. Under --fp16 a non-finite gradient norm skips the
-        update and halves the loss scale, then raises OverflowError like fairseq so that
-        Controller.train_step's handler (reference controller.py:368-371) finally has a raiser."""
+        """One fused pass over the owned elements. The kernels take the overflow flag from device
+        memory, so the update is queued first and only then is the flag read back for the loss scaler:
+        under --fp16 a non-finite gradient norm leaves parameters and state untouched, halves the loss
+        scale and raises OverflowError like fairseq, so that Controller.train_step's handler (reference
+        controller.py:368-371) finally has a raiser."""
+        fused = getattr(self.dp, 'fused', False)
+        if self._skip is None or (fused and not getattr(self, '_fused_ready', False)):
+            self.clip_grad_norm(0.0)
+        t = self.step_count + 1
+        if fused:
+            b1, b2 = self.hyper['betas']
+            self.dp.adam_allgather(self, math.sqrt(1 - b2 ** t) / (1 - b1 ** t))
+        elif self._native is not None:
+            self.step_count = t
+            self._native.update(self._pending_mult(), self._skip)
+            self.step_count = t - 1
         overflow = False
         if self.scaler is not None:
-            if self._skip is None:
-                self.clip_grad_norm(0.0)
             overflow = bool(self._skip.item())
             self.scaler.update(overflow)
             if overflow:
+                self._mult, self._mult_dev, self._skip = 1.0, None, None
                 if self.scaler.loss_scale <= self.scaler.min_loss_scale:
                     raise FloatingPointError(
                         'Minimum loss scale reached ({}). Your loss is probably exploding.'.format(
                             self.scaler.min_loss_scale))
                 raise OverflowError('setting loss scale to: ' + str(self.scaler.loss_scale))
-        self.step_count += 1
-        mult = self._pending_mult()
-        g = self._owned(self.buffer.flat_grad)
-        out = self._owned(self.buffer.flat_param)
-        if self._native is not None:
-            self._native.update(mult)
-        else:
+        self.step_count = t
+        if not fused and self._native is None:
+            mult = self._pending_mult()
+            g = self._owned(self.buffer.flat_grad)
+            out = self._owned(self.buffer.flat_param)
             if torch.is_tensor(mult):
                 g32 = g.float() * mult
             else:

@@ -175,6 +175,39 @@ HS_API int hs_attention_bwd(const void* qkv, const float* mask, const void* ctx,
                             void* dqkv, int B, int S, int heads, int H, float dropout_p, const long long* seed,
                             unsigned site, int dtype, hs_stream_t stream);
 
+/* ---- fused data-parallel gradient path over NVLink peer memory (csrc/comm_sm100.cu) ------------------- */
+/* Replaces DDP's bucketed NCCL all-reduce (controller.py:78-86, N4) + multiply_grads + clip_grad_norm +
+ * Adam.step on every rank (optim.py:59-70,162-231, K15-K17) -- SURVEY.md W1. W <= 16 ranks of one node.
+ * Buffers come from hs_ipc_alloc and are mapped into every peer with hs_ipc_open; *_ptrs are HOST arrays
+ * of W device pointers indexed by rank (entry [rank] is the local buffer). Ownership is cyclic by chunk:
+ * chunk c of the flat buffers belongs to rank c % W. Flags in the signal pads carry `epoch` (the update
+ * number, strictly increasing); pads are hs_dp_signal_words() 32-bit words, zero-initialised. */
+HS_API int hs_ipc_alloc(size_t bytes, void** ptr, unsigned char* handle64);
+HS_API int hs_ipc_open(const unsigned char* handle64, void** ptr);
+HS_API int hs_ipc_close(void* ptr);
+HS_API int hs_ipc_free(void* ptr);
+HS_API int hs_dp_signal_words(int W, int max_buckets);
+/* One bucket = chunks [chunk_begin, chunk_end). Announces the bucket to all peers, waits for theirs, then
+ * sums the W copies of every owned chunk straight from peer memory into the local fp32 gradient and adds
+ * the squared sum into *sumsq_accum. Launch on a side stream as soon as the bucket's gradients are final. */
+HS_API int hs_dp_reduce_scatter(void* const* grad_ptrs, void* const* sig_ptrs, int rank, int W,
+                                long long chunk_begin, long long chunk_end, int chunk, int slot, unsigned epoch,
+                                float* sumsq_accum, int nblocks, hs_stream_t stream);
+/* All ranks exchange their norm partial through the pads and derive identical
+ * out4 = [grad_norm, multiplier * clip coefficient, overflow flag, global sum of squares]; *skip_out = flag. */
+HS_API int hs_dp_norm_exchange(void* const* sig_ptrs, int rank, int W, unsigned epoch, float* sumsq_accum,
+                               float mult_host, const float* mult_dev, float max_norm, float* out4, int* skip_out,
+                               hs_stream_t stream);
+/* Adam (math of optim.py:162-231) on the owned chunks; the updated 16-bit parameters are stored into all W
+ * parameter buffers (the all-gather). scalars = out4 of hs_dp_norm_exchange. */
+HS_API int hs_dp_adam_allgather(const float* grad, float* master, float* exp_avg, float* exp_avg_sq,
+                                void* const* param_ptrs, void* const* sig_ptrs, int rank, int W, long long nblocks,
+                                int chunk, int out_dtype, float lr, float beta1, float beta2, float eps,
+                                float weight_decay, float step_factor, const float* scalars, const float* hyper_dev,
+                                unsigned epoch, unsigned int* done_counter, int grid_blocks, hs_stream_t stream);
+/* Returns (on the stream) once every rank's parameter stores of update `epoch` have landed locally. */
+HS_API int hs_dp_wait_params(void* const* sig_ptrs, int rank, int W, unsigned epoch, hs_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,91 @@
+"""Worker for the multi-process data-parallel tests (launched by torch.distributed.run).
+
+Trains a tiny BERT for a few updates with the requested --dp-backend and lets rank 0 save the final
+parameters + the per-step log, so the test can compare backends with each other and with a
+single-process run over the concatenated batch. Works on CPU (Gloo) and on GPUs (NCCL / fused NVLink).
+"""
+import argparse
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+import torch
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--backend', default='nccl')
+    ap.add_argument('--out', required=True)
+    ap.add_argument('--cpu', action='store_true')
+    ap.add_argument('--steps', type=int, default=3)
+    ap.add_argument('--precision', default='fp32')
+    ap.add_argument('--hidden', type=int, default=64)
+    ap.add_argument('--seq', type=int, default=32)
+    ap.add_argument('--update-freq', type=int, default=1)
+    ap.add_argument('--optimizer', default='adam')
+    a = ap.parse_args()
+
+    rank = int(os.environ.get('RANK', 0))
+    world = int(os.environ.get('WORLD_SIZE', 1))
+    local = int(os.environ.get('LOCAL_RANK', 0))
+    from hetseq_b200 import options, registry
+    from hetseq_b200.controller import Controller
+    from hetseq_b200.data.bert_dataset import SyntheticBertData
+    from hetseq_b200.parallel import distributed_utils
+
+    tmp = os.path.dirname(a.out)
+    cfg = dict(vocab_size=1000, hidden_size=a.hidden, num_hidden_layers=2, num_attention_heads=a.hidden // 64 or 1,
+               intermediate_size=4 * a.hidden, hidden_act='gelu', hidden_dropout_prob=0.0,
+               attention_probs_dropout_prob=0.0, max_position_embeddings=128, type_vocab_size=2, initializer_range=0.02)
+    cfg_path = os.path.join(tmp, 'cfg_%d.json' % rank)
+    with open(cfg_path, 'w') as f:
+        json.dump(cfg, f)
+    argv = ['--config_file', cfg_path, '--max-sentences', '4', '--synthetic-data', '--lr', '1e-3', '--no-save',
+            '--log-format', 'none', '--distributed-world-size', str(world), '--distributed-rank', str(rank),
+            '--device-id', str(local), '--dp-backend', a.backend, '--save-dir', tmp, '--clip-norm', '1.0',
+            '--fast-stat-sync', '--bucket-cap-mb', '1']
+    if a.optimizer == 'adam':
+        argv += ['--adam-betas', '(0.9, 0.98)', '--weight-decay', '0.01']
+    if a.cpu:
+        argv.append('--cpu')
+    if a.precision == 'fp16':
+        argv.append('--fp16')
+    elif a.precision == 'bf16':
+        argv.append('--bf16')
+    args = options.make_args('bert', a.optimizer, 'PolynomialDecayScheduler', argv)
+    if not a.cpu:
+        torch.cuda.set_device(local)
+    if world > 1:
+        args.distributed_init_method = 'env://'
+        distributed_utils.distributed_init(args)
+    torch.manual_seed(1)
+    task = registry.lookup('task', 'bert').setup_task(args)
+    model = task.build_model(args)
+    ctl = Controller(args, task, model)
+    ctl.optimizer
+    ds = SyntheticBertData(4096, a.seq, 5, 1000, seed=11)
+    log = []
+    for step in range(a.steps):
+        samples = []
+        for u in range(a.update_freq):
+            # global micro-batch index -> the same data no matter how many ranks split it
+            gidx = (step * a.update_freq + u) * world + rank
+            samples.append(ds.fetch_rows(list(range(gidx * 4, gidx * 4 + 4))))
+        out = ctl.train_step(samples)
+        log.append(None if out is None else {'loss': out['loss'], 'gnorm': ctl.get_meter('gnorm').val,
+                                            'nsentences': out['nsentences']})
+    consistent = ctl.dp.check_params_consistent()
+    state = ctl.optimizer.state_dict()   # collective when sharded
+    if rank == 0:
+        torch.save({'params': ctl.buffer.flat_param.detach().float().cpu(), 'log': log, 'consistent': consistent,
+                    'backend': ctl.dp.name, 'opt_state': {k: {n: (t.cpu() if torch.is_tensor(t) else t) for n, t in v.items()}
+                                                            for k, v in state['state'].items()}}, a.out)
+    ctl.close()
+    if world > 1:
+        torch.distributed.destroy_process_group()
+
+
+if __name__ == '__main__':
+    main()
