@@ -332,6 +332,9 @@ class NativeBert(object):
         self.bert.native = self
         if hasattr(model, 'cls') and hasattr(model, 'bert') and model.__class__.__name__ == 'BertForPreTraining':
             model.native = self
+            # the tied decoder / word-embedding matrix gets two gradient contributions per backward
+            # (decoder wgrad, then the embedding scatter): report it ready only after the second
+            buffer.set_expected_notifications(self.bert.embeddings.word_embeddings.weight, 2)
 
     def _pack(self, params, shape):
         buf, i0 = params[0]._hs_flat

@@ -45,7 +45,7 @@ class LocalBackend(object):
         pass
 
     def begin_micro_batch(self, index: int, is_last: bool):
-        pass
+        self.buffer.reset_ready_counts()
 
     def finish_gradients(self, optimizer):
         pass
@@ -82,6 +82,9 @@ class AllReduceBackend(LocalBackend):
         self._launched = [False] * len(self.buckets)
         self._handles = []
         self._armed = False
+        # debugging aid: reduce everything after backward instead of bucket by bucket during it
+        import os
+        self._no_overlap = bool(int(os.environ.get('HETSEQ_DP_NO_OVERLAP', '0')))
         buffer.ready_callback = self._on_param_ready
 
     def broadcast_params(self):
@@ -92,7 +95,9 @@ class AllReduceBackend(LocalBackend):
         self._handles = []
 
     def begin_micro_batch(self, index: int, is_last: bool):
+        self.buffer.reset_ready_counts()
         self._armed = bool(is_last)
+        self._seen = set()
         if is_last:
             self._pending = [len(p) for p in self._bucket_params]
             self._launched = [False] * len(self.buckets)
@@ -104,8 +109,11 @@ class AllReduceBackend(LocalBackend):
 
     def _on_param_ready(self, i: int):
         """Called (from autograd hooks or native ops) when parameter i's gradient is final."""
-        if not self._armed:
+        if not self._armed or self._no_overlap:
             return
+        if i in self._seen:
+            raise RuntimeError('parameter {} reported gradient-ready twice in one backward pass'.format(i))
+        self._seen.add(i)
         for b in self._param_buckets[i]:
             self._pending[b] -= 1
             if self._pending[b] == 0 and not self._launched[b]:

@@ -95,6 +95,10 @@ class FlatParamBuffer(object):
         #: called with a parameter index once that parameter's gradient is final for the current
         #: micro-batch; data-parallel backends use it to start reducing a bucket during backward
         self.ready_callback: Optional[Callable[[int], None]] = None
+        #: how many gradient contributions a parameter receives from ops that write main_grad themselves
+        #: (2 for BERT's tied decoder / word-embedding matrix); the callback fires on the last one
+        self._expected_notifications: List[int] = [1] * len(self.params)
+        self._notifications: List[int] = [0] * len(self.params)
         self.zero_grad()
 
     # -- gradient plumbing ----------------------------------------------------------------------
@@ -102,7 +106,11 @@ class FlatParamBuffer(object):
         fold = self.param_dtype != self.grad_dtype
 
         def hook(p):
-            if fold and p.grad is not None:
+            if fold:
+                # autograd also runs this hook when an op returned no gradient for the parameter (the
+                # native ops write main_grad themselves and report through notify_ready): nothing to do
+                if p.grad is None:
+                    return
                 g = self.main_grads[i]
                 if self._written[i]:
                     g.add_(p.grad)
@@ -115,9 +123,20 @@ class FlatParamBuffer(object):
         return hook
 
     def notify_ready(self, p: torch.nn.Parameter) -> None:
-        """For ops that wrote ``main_grad`` themselves (no autograd hook fires for them)."""
-        if self.ready_callback is not None:
-            self.ready_callback(p._hs_flat[1])
+        """For ops that wrote ``main_grad`` themselves (no autograd hook fires for them). A parameter
+        used by several such ops (tied weights) is reported once, after its last contribution."""
+        i = p._hs_flat[1]
+        self._notifications[i] += 1
+        if self._notifications[i] >= self._expected_notifications[i] and self.ready_callback is not None:
+            self.ready_callback(i)
+
+    def set_expected_notifications(self, p: torch.nn.Parameter, n: int) -> None:
+        self._expected_notifications[p._hs_flat[1]] = int(n)
+
+    def reset_ready_counts(self) -> None:
+        """Called at the start of every micro-batch's backward."""
+        for i in range(len(self._notifications)):
+            self._notifications[i] = 0
 
     def grad_target(self, p: torch.nn.Parameter) -> Tuple[torch.Tensor, bool]:
         """(main_grad view, accumulate?) for an op that writes the gradient itself."""

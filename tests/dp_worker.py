@@ -74,6 +74,11 @@ def main():
             gidx = (step * a.update_freq + u) * world + rank
             samples.append(ds.fetch_rows(list(range(gidx * 4, gidx * 4 + 4))))
         out = ctl.train_step(samples)
+        if os.environ.get('HS_DP_DEBUG'):
+            fp, fg = ctl.buffer.flat_param.float(), ctl.buffer.flat_grad.float()
+            print('DBG rank %d step %d param sum %.10e abs %.10e | grad sum %.10e abs %.10e | gnorm %r' % (
+                rank, step, fp.double().sum().item(), fp.double().abs().sum().item(), fg.double().sum().item(),
+                fg.double().abs().sum().item(), ctl.get_meter('gnorm').val), force=True, flush=True)
         log.append(None if out is None else {'loss': out['loss'], 'gnorm': ctl.get_meter('gnorm').val,
                                             'nsentences': out['nsentences']})
     consistent = ctl.dp.check_params_consistent()
