@@ -79,8 +79,10 @@ __device__ __forceinline__ void wait_flag(const uint32_t* p, uint32_t want, cons
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(DP_THREADS)
 dp_reduce_scatter_kernel(PeerTable grads, PeerTable sigs, int rank, int W, long long chunk_begin,
-                         long long chunk_end, int chunk, int slot, uint32_t epoch, float* __restrict__ sumsq_accum) {
+                         long long chunk_end, int chunk, int slot, uint32_t epoch, const uint32_t* __restrict__ epoch_dev,
+                         float* __restrict__ sumsq_accum) {
   __shared__ float red[32];
+  if (epoch_dev != nullptr) epoch = *epoch_dev;
   // 1. announce + wait (block 0 announces; every block waits on its own before touching peer data)
   if (blockIdx.x == 0 && threadIdx.x < W) {
     __threadfence_system();
@@ -126,10 +128,11 @@ dp_reduce_scatter_kernel(PeerTable grads, PeerTable sigs, int rank, int W, long 
 
 // out = [grad_norm, multiplier (incl. clip), skip flag (as float), global sum of squares]
 __global__ void __launch_bounds__(32)
-dp_norm_exchange_kernel(PeerTable sigs, int rank, int W, uint32_t epoch, float* __restrict__ sumsq_accum,
-                        float mult_host, const float* __restrict__ mult_dev, float max_norm,
-                        float* __restrict__ out, int* __restrict__ skip_out) {
+dp_norm_exchange_kernel(PeerTable sigs, int rank, int W, uint32_t epoch, const uint32_t* __restrict__ epoch_dev,
+                        float* __restrict__ sumsq_accum, float mult_host, const float* __restrict__ mult_dev,
+                        float max_norm, float* __restrict__ out, int* __restrict__ skip_out) {
   const int t = threadIdx.x;
+  if (epoch_dev != nullptr) epoch = *epoch_dev;
   const float mine = *sumsq_accum;
   if (t < W) {
     uint32_t* pad = reinterpret_cast<uint32_t*>(sigs.ptr[t]);
@@ -170,7 +173,9 @@ __global__ void __launch_bounds__(DP_THREADS)
 dp_adam_allgather_kernel(const float* __restrict__ grad, float* __restrict__ master, float* __restrict__ m,
                          float* __restrict__ v, PeerTable params, PeerTable sigs, int rank, int W,
                          long long nblocks, int chunk, DpAdamHyper h, const float* __restrict__ scalars,
-                         const float* __restrict__ hyper_dev, uint32_t epoch, unsigned int* __restrict__ done_counter) {
+                         const float* __restrict__ hyper_dev, uint32_t epoch, const uint32_t* __restrict__ epoch_dev,
+                         unsigned int* __restrict__ done_counter) {
+  if (epoch_dev != nullptr) epoch = *epoch_dev;
   const bool skip = scalars[2] != 0.f;
   if (!skip) {
     const float mult = scalars[1];
@@ -231,7 +236,8 @@ dp_adam_allgather_kernel(const float* __restrict__ grad, float* __restrict__ mas
 }
 
 __global__ void __launch_bounds__(32)
-dp_wait_params_kernel(PeerTable sigs, int rank, int W, uint32_t epoch) {
+dp_wait_params_kernel(PeerTable sigs, int rank, int W, uint32_t epoch, const uint32_t* __restrict__ epoch_dev) {
+  if (epoch_dev != nullptr) epoch = *epoch_dev;
   if (threadIdx.x < W)
     wait_flag(reinterpret_cast<const uint32_t*>(sigs.ptr[rank]) + sig_param_ready(threadIdx.x), epoch,
               "updated parameters", threadIdx.x);
@@ -272,7 +278,7 @@ extern "C" int hs_dp_signal_words(int W, int max_buckets) { return 4 * W + max_b
 // ---- kernels ----------------------------------------------------------------------------------------
 extern "C" int hs_dp_reduce_scatter(void* const* grad_ptrs, void* const* sig_ptrs, int rank, int W,
                                     long long chunk_begin, long long chunk_end, int chunk, int slot, unsigned epoch,
-                                    float* sumsq_accum, int nblocks, hs_stream_t stream) {
+                                    const unsigned* epoch_dev, float* sumsq_accum, int nblocks, hs_stream_t stream) {
   PeerTable g, s;
   if (fill_table(&g, grad_ptrs, W) || fill_table(&s, sig_ptrs, W)) return 1;
   if (chunk % 4 != 0 || chunk_end <= chunk_begin || rank < 0 || rank >= W) {
@@ -282,16 +288,17 @@ extern "C" int hs_dp_reduce_scatter(void* const* grad_ptrs, void* const* sig_ptr
   const long long owned = (chunk_end - chunk_begin + W - 1) / W;
   int grid = nblocks > 0 ? nblocks : 64;
   if (grid > owned) grid = static_cast<int>(owned < 1 ? 1 : owned);
-  dp_reduce_scatter_kernel<<<grid, DP_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(g, s, rank, W, chunk_begin, chunk_end, chunk, slot, epoch, sumsq_accum);
+  dp_reduce_scatter_kernel<<<grid, DP_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(g, s, rank, W, chunk_begin, chunk_end, chunk, slot, epoch, epoch_dev, sumsq_accum);
   return post_launch("dp_reduce_scatter_kernel");
 }
 
-extern "C" int hs_dp_norm_exchange(void* const* sig_ptrs, int rank, int W, unsigned epoch, float* sumsq_accum,
+extern "C" int hs_dp_norm_exchange(void* const* sig_ptrs, int rank, int W, unsigned epoch, const unsigned* epoch_dev,
+                                   float* sumsq_accum,
                                    float mult_host, const float* mult_dev, float max_norm, float* out4, int* skip_out,
                                    hs_stream_t stream) {
   PeerTable s;
   if (fill_table(&s, sig_ptrs, W)) return 1;
-  dp_norm_exchange_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(s, rank, W, epoch, sumsq_accum, mult_host, mult_dev, max_norm, out4, skip_out);
+  dp_norm_exchange_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(s, rank, W, epoch, epoch_dev, sumsq_accum, mult_host, mult_dev, max_norm, out4, skip_out);
   return post_launch("dp_norm_exchange_kernel");
 }
 
@@ -299,7 +306,8 @@ extern "C" int hs_dp_adam_allgather(const float* grad, float* master, float* exp
                                     void* const* param_ptrs, void* const* sig_ptrs, int rank, int W, long long nblocks,
                                     int chunk, int out_dtype, float lr, float beta1, float beta2, float eps,
                                     float weight_decay, float step_factor, const float* scalars, const float* hyper_dev,
-                                    unsigned epoch, unsigned int* done_counter, int grid_blocks, hs_stream_t stream) {
+                                    unsigned epoch, const unsigned* epoch_dev, unsigned int* done_counter, int grid_blocks,
+                                    hs_stream_t stream) {
   PeerTable p, s;
   if (fill_table(&p, param_ptrs, W) || fill_table(&s, sig_ptrs, W)) return 1;
   if (chunk % 4 != 0 || nblocks <= 0) { set_last_error("hs_dp_adam_allgather: bad layout"); return 1; }
@@ -308,16 +316,17 @@ extern "C" int hs_dp_adam_allgather(const float* grad, float* master, float* exp
   if (grid > nblocks) grid = static_cast<int>(nblocks);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (out_dtype == HS_F16)
-    dp_adam_allgather_kernel<__half><<<grid, DP_THREADS, 0, st>>>(grad, master, exp_avg, exp_avg_sq, p, s, rank, W, nblocks, chunk, h, scalars, hyper_dev, epoch, done_counter);
+    dp_adam_allgather_kernel<__half><<<grid, DP_THREADS, 0, st>>>(grad, master, exp_avg, exp_avg_sq, p, s, rank, W, nblocks, chunk, h, scalars, hyper_dev, epoch, epoch_dev, done_counter);
   else if (out_dtype == HS_BF16)
-    dp_adam_allgather_kernel<__nv_bfloat16><<<grid, DP_THREADS, 0, st>>>(grad, master, exp_avg, exp_avg_sq, p, s, rank, W, nblocks, chunk, h, scalars, hyper_dev, epoch, done_counter);
+    dp_adam_allgather_kernel<__nv_bfloat16><<<grid, DP_THREADS, 0, st>>>(grad, master, exp_avg, exp_avg_sq, p, s, rank, W, nblocks, chunk, h, scalars, hyper_dev, epoch, epoch_dev, done_counter);
   else { set_last_error("hs_dp_adam_allgather: parameters must be f16 or bf16"); return 1; }
   return post_launch("dp_adam_allgather_kernel");
 }
 
-extern "C" int hs_dp_wait_params(void* const* sig_ptrs, int rank, int W, unsigned epoch, hs_stream_t stream) {
+extern "C" int hs_dp_wait_params(void* const* sig_ptrs, int rank, int W, unsigned epoch, const unsigned* epoch_dev,
+                                 hs_stream_t stream) {
   PeerTable s;
   if (fill_table(&s, sig_ptrs, W)) return 1;
-  dp_wait_params_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(s, rank, W, epoch);
+  dp_wait_params_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(s, rank, W, epoch, epoch_dev);
   return post_launch("dp_wait_params_kernel");
 }

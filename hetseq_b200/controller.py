@@ -61,6 +61,14 @@ class Controller(object):
 
         self.fast_stat_sync = args.fast_stat_sync
         self.step_timer = CudaEventTimer(use_cuda=self.cuda)
+        # HETSEQ_PHASE_TIMING=1: CUDA-event timing of the phases of every update (printed by close())
+        self._phase_timing = self.cuda and bool(int(os.environ.get('HETSEQ_PHASE_TIMING', '0')))
+        self._phase_events = []
+        # --cuda-graph: capture the device part of an update once, replay it afterwards
+        self._graph_enabled = bool(getattr(args, 'cuda_graph', False)) and self.cuda
+        self._graph, self._graph_key, self._graph_warmup, self._capturing = None, None, 0, False
+        self._static_sample, self._static_out = None, None
+        self._stats_host = None
         self.init_meters(args)
 
     # -- meters -----------------------------------------------------------------------------------
@@ -140,6 +148,9 @@ class Controller(object):
             pos = {id(p): i for i, p in enumerate(canonical)}
             self._buffer.canonical_index = [pos[id(p)] for p in self._buffer.params]
             self._dp = data_parallel.build_backend(args, self._buffer)
+            if self._graph_enabled and self._dp.name in ('nccl', 'sharded-allreduce'):
+                print('| --cuda-graph is only used with the local and fused-nvlink gradient paths; running eagerly')
+                self._graph_enabled = False
             self._dp.broadcast_params()
             self._attach_native()
 
@@ -261,62 +272,126 @@ class Controller(object):
 
     # -- the hot loop -------------------------------------------------------------------------------
     def train_step(self, samples, dummy_batch=False, raise_oom=False):
-        """forward / backward over the micro-batches of one update, then reduce, clip and step."""
+        """forward / backward over the micro-batches of one update, then reduce, clip and step.
+
+        Device work and host bookkeeping are separated: ``_device_step`` only queues work (no host
+        synchronisation, no host values that change between updates baked into kernels), which is what
+        allows ``--cuda-graph`` to capture it once and replay it; the host then makes ONE read of a small
+        result vector and updates meters, loss scale and the LR schedule."""
         if self._dummy_batch is None:
             self._dummy_batch = samples[0]
 
         self._set_seed()
         model = self.model
         model.train()
-        self.zero_grad()
-        dp, opt = self.dp, self.optimizer
-
         if not dummy_batch:
             self.meters['train_wall'].start()
             self.step_timer.start()
 
-        # host-side integer stats + device-side loss sum; nothing here synchronises
-        n_sample_size = n_sentences = n_tokens = 0
-        loss_sum = torch.zeros((), dtype=torch.float32, device=self.device)
-        logging_outputs, ooms = [], 0
-        dp.begin_update(len(samples))
-        for i, sample in enumerate(samples):
-            prepared = self._prepare_sample(sample)
-            if prepared is None:
-                # uneven shards: run on the cached dummy batch and ignore its gradients so that
-                # every rank still takes part in the reduction (controller.py:237-241)
-                prepared = self._prepare_sample(self._dummy_batch)
-                ignore_grad = True
-            else:
-                ignore_grad = False
-            sample_dev, stats = prepared
-            dp.begin_micro_batch(i, is_last=(i == len(samples) - 1))
-            try:
-                loss, sample_size, logging_output = self.task.train_step(
-                    sample_dev, model, opt, ignore_grad, stats=stats)
-            except RuntimeError as e:
-                if 'out of memory' in str(e):
-                    raise RuntimeError('ran out of memory with exception') from e
-                raise
-            if not ignore_grad:
-                logging_outputs.append(logging_output)
-                n_sample_size += sample_size
-                n_sentences += logging_output.get('nsentences', 0)
-                n_tokens += logging_output.get('ntokens', 0)
-                weight = logging_output.get('nsentences', 1) if self.args.sample_size_mode == 'batch' else 1.0
-                loss_sum = loss_sum + logging_output['loss'].float() * weight
+        # ---- host -> device ---------------------------------------------------------------------
+        prepared, host_stats = [], [0, 0, 0]          # sample_size, nsentences, ntokens
+        for sample in samples:
+            p = self._prepare_sample(sample)
+            ignore = p is None
+            if ignore:
+                # uneven shards: run on the cached dummy batch and ignore its gradients so that every rank
+                # still takes part in the reduction (controller.py:237-241)
+                p = self._prepare_sample(self._dummy_batch)
+            sample_dev, stats = p
+            prepared.append((sample_dev, stats, ignore))
+            if not ignore:
+                host_stats[0] += self.task.sample_size(sample_dev, stats[0])
+                host_stats[1] += stats[0]
+                host_stats[2] += stats[1]
 
+        # ---- device ---------------------------------------------------------------------------------
+        graphable = (self._graph_enabled and not dummy_batch and len(prepared) == 1 and not prepared[0][2])
+        try:
+            if graphable:
+                readback = self._graphed_device_step(prepared[0], host_stats)
+            else:
+                readback = self._device_step(prepared, host_stats, device_stats_sync=True)
+        except RuntimeError as e:
+            if 'out of memory' in str(e):
+                raise RuntimeError('ran out of memory with exception') from e
+            raise
         if dummy_batch:
             return None
 
+        # ---- the single device->host read of the update --------------------------------------------------
+        if graphable and self._sync_stats():
+            # inside a captured graph the sample size is taken as world x local (all ranks hold full
+            # batches); the logging statistics are summed here, outside the graph
+            comm = readback[:6].clone()
+            torch.distributed.all_reduce(comm)
+            readback = torch.cat([comm, readback[6:]])
+        sample_size, nsentences, loss_total, nll_total, ntokens, ooms, gnorm, skip = readback.tolist()
+        opt = self.optimizer
+        logging_output = None
+        try:
+            opt.finish_update(bool(skip) and opt.scaler is not None)
+            self.set_num_updates(self.get_num_updates() + 1)
+            self.task.update_step(self._num_updates)
+            self._prev_grad_norm = gnorm
+            # like the fast path of the reference (controller.py:299-304) losses are logged as
+            # sum / (sample_size * ln 2); in 'batch' mode the sum is weighted by sentences so this is
+            # the true per-sentence mean in base 2
+            denom = max(sample_size, 1e-12) * math.log(2)
+            loss_avg = loss_total / denom
+            logging_output = {'loss': loss_avg, 'nll_loss': nll_total / denom, 'ntokens': ntokens,
+                              'nsentences': nsentences, 'sample_size': sample_size}
+            self.meters['wps'].update(ntokens)
+            self.meters['ups'].update(1.)
+            self.meters['wpb'].update(ntokens)
+            self.meters['bsz'].update(nsentences)
+            self.meters['gnorm'].update(gnorm)
+            self.meters['clip'].update(1. if gnorm > self.args.clip_norm and self.args.clip_norm > 0 else 0.)
+            self.meters['oom'].update(ooms)
+            self.meters['train_loss'].update(loss_avg, sample_size)
+            if 'loss_scale' in self.meters:
+                self.meters['loss_scale'].reset()
+                self.meters['loss_scale'].update(opt.loss_scale)
+        except OverflowError as e:
+            print('| WARNING: overflow detected, ' + str(e))
+            logging_output = None
+
+        self.step_timer.stop()
+        self.meters['train_wall'].stop()
+        return logging_output
+
+    def _device_step(self, prepared, host_stats, device_stats_sync=True):
+        """Queue one whole update on the device and return the 8-element result vector
+        [sample_size, nsentences, loss_sum, nll_sum, ntokens, ooms, grad_norm, overflow] (fp64, device)."""
+        model, dp, opt = self._model, self.dp, self.optimizer
+        self.zero_grad()
+        marks = [self._mark()] if (self._phase_timing and not self._capturing) else None
+        loss_sum = torch.zeros((), dtype=torch.float32, device=self.device)
+        dp.begin_update(len(prepared))
+        for i, (sample_dev, stats, ignore_grad) in enumerate(prepared):
+            dp.begin_micro_batch(i, is_last=(i == len(prepared) - 1))
+            loss, sample_size, logging_output = self.task.train_step(sample_dev, model, opt, ignore_grad, stats=stats)
+            if not ignore_grad:
+                weight = logging_output.get('nsentences', 1) if self.args.sample_size_mode == 'batch' else 1.0
+                loss_sum = loss_sum + logging_output['loss'].float() * weight
+        if marks is not None:
+            marks.append(self._mark())      # forward + backward enqueued
         dp.finish_gradients(opt)
+        if marks is not None:
+            marks.append(self._mark())      # gradient reduction complete
 
         # ---- stats: [sample_size, nsentences, loss, nll_loss, ntokens, ooms] like controller.py:292-314
-        stats_vec = torch.zeros(6, dtype=torch.float64, device=self.device)
-        stats_vec[0], stats_vec[1], stats_vec[4], stats_vec[5] = n_sample_size, n_sentences, n_tokens, ooms
-        stats_vec[2] = loss_sum.double()
-        stats_vec[3] = loss_sum.double()
-        if self._sync_stats():
+        multi = self._sync_stats()
+        # host integers travel through a pinned staging vector (re-read by a captured graph on each replay)
+        if self._stats_host is None:
+            self._stats_host = torch.zeros(6, dtype=torch.float64)
+            if self.cuda:
+                self._stats_host = self._stats_host.pin_memory()
+        self._stats_host[0], self._stats_host[1], self._stats_host[4] = host_stats[0], host_stats[1], host_stats[2]
+        stats_vec = self._stats_host.to(self.device, non_blocking=True)
+        loss64 = loss_sum.double()
+        stats_vec = torch.cat([stats_vec[:2], loss64.reshape(1), loss64.reshape(1), stats_vec[4:]])
+        world = float(self.args.distributed_world_size if multi else 1)
+        if multi and device_stats_sync:
             if self.fast_stat_sync:
                 comm = stats_vec if stats_vec.device == distributed_utils.comm_device() else stats_vec.cpu()
                 torch.distributed.all_reduce(comm)
@@ -333,51 +408,60 @@ class Controller(object):
                     'Fatal error: gradients are inconsistent between workers'
                 stats_vec = torch.tensor([sum(g[0][k] for g in gathered) for k in range(6)],
                                          dtype=torch.float64, device=self.device)
-
-        logging_output = None
-        try:
             sample_size_dev = stats_vec[0]
-            # normalise grads by sample size (controller.py:338-339); the backend already made them
-            # the mean over ranks, so the factor is world / sample_size like the reference's
-            world = float(self.args.distributed_world_size if self._sync_stats() else 1)
-            opt.multiply_grads(torch.where(sample_size_dev > 0, world / sample_size_dev.clamp(min=1e-12),
-                                           torch.ones_like(sample_size_dev)).float())
-            grad_norm = opt.clip_grad_norm(self.args.clip_norm)
-            opt.step()
-            self.set_num_updates(self.get_num_updates() + 1)
-            self.task.update_step(self._num_updates)
+        elif multi:
+            sample_size_dev = stats_vec[0] * world     # captured graph: all ranks hold equal, full batches
+        else:
+            sample_size_dev = stats_vec[0]
 
-            # ---- the single device->host read of the step
-            readback = torch.cat([stats_vec, grad_norm.detach().double().reshape(1)]).tolist()
-            sample_size, nsentences, loss_total, nll_total, ntokens, ooms, gnorm = readback
-            self._prev_grad_norm = gnorm
-            # like the fast path of the reference (controller.py:299-304) losses are logged as
-            # sum / (sample_size * ln 2); in 'batch' mode the sum is weighted by sentences so this is
-            # the true per-sentence mean in base 2
-            denom = max(sample_size, 1e-12) * math.log(2)
-            loss_avg = loss_total / denom
-            logging_output = {'loss': loss_avg, 'nll_loss': nll_total / denom,
-                              'ntokens': ntokens, 'nsentences': nsentences, 'sample_size': sample_size}
+        # normalise grads by sample size (controller.py:338-339); the backend already made them the mean
+        # over ranks, so the factor is world / sample_size like the reference's
+        opt.multiply_grads(torch.where(sample_size_dev > 0, world / sample_size_dev.clamp(min=1e-12),
+                                       torch.ones_like(sample_size_dev)).float())
+        grad_norm = opt.clip_grad_norm(self.args.clip_norm)
+        if marks is not None:
+            marks.append(self._mark())      # stats sync + norm
+        opt.launch_update()
+        if marks is not None:
+            marks.append(self._mark())      # update (+ all-gather)
+            self._phase_events.append(marks)
+        skip = opt._skip.double().reshape(1) if opt._skip is not None else torch.zeros(1, dtype=torch.float64, device=self.device)
+        return torch.cat([stats_vec, grad_norm.detach().double().reshape(1), skip])
 
-            self.meters['wps'].update(ntokens)
-            self.meters['ups'].update(1.)
-            self.meters['wpb'].update(ntokens)
-            self.meters['bsz'].update(nsentences)
-            self.meters['gnorm'].update(gnorm)
-            self.meters['clip'].update(1. if gnorm > self.args.clip_norm and self.args.clip_norm > 0 else 0.)
-            self.meters['oom'].update(ooms)
-            self.meters['train_loss'].update(loss_avg, sample_size)
-            if 'loss_scale' in self.meters:
-                self.meters['loss_scale'].reset()
-                self.meters['loss_scale'].update(opt.loss_scale)
-        except OverflowError as e:
-            print('| WARNING: overflow detected, ' + str(e))
-            self.zero_grad()
-            logging_output = None
-
-        self.step_timer.stop()
-        self.meters['train_wall'].stop()
-        return logging_output
+    # -- CUDA graph capture of the device step -----------------------------------------------------------
+    def _graphed_device_step(self, prepared_one, host_stats):
+        """Replay (after a few eager warm-up updates: capture) the whole device step as one CUDA graph.
+        Inputs are copied into static buffers; per-update scalars (lr, bias correction, loss scale, dropout
+        seed, NVLink epoch) live in device memory that the graph re-reads."""
+        sample_dev, stats, _ = prepared_one
+        key = tuple((tuple(t.shape), t.dtype) for t in sample_dev) + (tuple(host_stats[:2]),)
+        if self._graph is not None and key != self._graph_key:
+            return self._device_step([prepared_one], host_stats, device_stats_sync=True)   # odd-shaped batch: eager
+        if self._graph is None:
+            self._graph_warmup += 1
+            if self._graph_warmup <= 3:
+                return self._device_step([prepared_one], host_stats, device_stats_sync=True)
+            # capture
+            self._graph_key = key
+            self._static_sample = [t.clone() for t in sample_dev]
+            torch.cuda.synchronize()
+            self._graph = torch.cuda.CUDAGraph()
+            self._capturing = True
+            try:
+                with torch.cuda.graph(self._graph):
+                    self._static_out = self._device_step([(self._static_sample, stats, False)], host_stats,
+                                                         device_stats_sync=False)
+            finally:
+                self._capturing = False
+            # the captured update was only recorded, not executed: fall through to a replay
+        for dst, src in zip(self._static_sample, sample_dev):
+            dst.copy_(src, non_blocking=True)
+        self.optimizer.write_host_scalars()
+        self._stats_host[0], self._stats_host[1], self._stats_host[4] = host_stats[0], host_stats[1], host_stats[2]
+        self._graph.replay()
+        # host-side Python state that _device_step normally leaves behind
+        self.optimizer._skip = self._static_out[7] != 0
+        return self._static_out
 
     def valid_step(self, sample):
         """Forward only (the reference never validates: train.py:93; available via --enable-validation)."""
@@ -437,6 +521,28 @@ class Controller(object):
     def _sync_stats(self):
         return self.args.distributed_world_size > 1 and torch.distributed.is_initialized()
 
+    def _mark(self):
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record()
+        return ev
+
+    def phase_report(self, skip=3):
+        """Mean milliseconds per phase over the recorded updates (first ``skip`` dropped)."""
+        if not self._phase_events:
+            return None
+        torch.cuda.synchronize()
+        names = ['fwd+bwd', 'reduce(exposed)', 'stats+norm', 'update+gather']
+        rows = [[m[k].elapsed_time(m[k + 1]) for k in range(len(m) - 1)] for m in self._phase_events[skip:] if len(m) == 5]
+        if not rows:
+            return None
+        return {n: sum(r[k] for r in rows) / len(rows) for k, n in enumerate(names)}
+
     def close(self):
+        if self._phase_timing:
+            rep = self.phase_report()
+            if rep is not None:
+                print('| phase timing (ms, rank {}): {}'.format(self.args.distributed_rank, ', '.join(
+                    '{}={:.3f}'.format(k, v) for k, v in rep.items())), force=True, flush=True) \
+                    if torch.distributed.is_initialized() else print('| phase timing (ms): {}'.format(rep), flush=True)
         if self._dp is not None:
             self._dp.close()

@@ -446,11 +446,16 @@ class BertForPreTraining(BertPreTrainedModel):
         self.native = None  # set by ops.bert_native.attach()
 
     def forward(self, input_ids, token_type_ids=None, attention_mask=None, masked_lm_labels=None,
-                next_sentence_label=None, checkpoint_activations=None):
+                next_sentence_label=None, mlm_rows=None, mlm_row_labels=None, checkpoint_activations=None):
+        """``mlm_rows`` / ``mlm_row_labels`` (optional, fixed capacity, padded with -1): flat indices of the
+        labelled positions and their labels, precomputed on the host by the task. They remove the
+        data-dependent ``nonzero`` (a device->host sync) from the step and give the MLM head a static shape,
+        which is what lets the whole step be captured in a CUDA graph."""
         ckpt = self.checkpoint_activations if checkpoint_activations is None else checkpoint_activations
         if self.native is not None and masked_lm_labels is not None and next_sentence_label is not None:
             return self.native.pretraining_loss(self, input_ids, token_type_ids, attention_mask,
-                                                masked_lm_labels, next_sentence_label, ckpt)
+                                                masked_lm_labels, next_sentence_label, ckpt,
+                                                mlm_rows=mlm_rows, mlm_row_labels=mlm_row_labels)
         sequence_output, pooled_output = self.bert(input_ids, token_type_ids, attention_mask,
                                                    output_all_encoded_layers=False,
                                                    checkpoint_activations=ckpt)
@@ -462,11 +467,15 @@ class BertForPreTraining(BertPreTrainedModel):
             prediction_scores, seq_relationship_score = self.cls(sequence_output, pooled_output)
             masked_lm_loss = F.cross_entropy(prediction_scores.view(-1, V).float(), labels, ignore_index=-1)
         else:
-            rows = torch.nonzero(labels != -1, as_tuple=False).squeeze(1)
+            if mlm_rows is not None:
+                rows, row_labels = mlm_rows.long().clamp(min=0), mlm_row_labels.long()
+            else:
+                rows = torch.nonzero(labels != -1, as_tuple=False).squeeze(1)
+                row_labels = labels.index_select(0, rows)
             hidden = sequence_output.reshape(-1, sequence_output.size(-1)).index_select(0, rows)
             prediction_scores = self.cls.predictions(hidden)
             seq_relationship_score = self.cls.seq_relationship(pooled_output)
-            masked_lm_loss = F.cross_entropy(prediction_scores.float(), labels.index_select(0, rows),
+            masked_lm_loss = F.cross_entropy(prediction_scores.float(), row_labels,
                                              ignore_index=-1) if rows.numel() > 0 else prediction_scores.sum() * 0
         next_sentence_loss = F.cross_entropy(seq_relationship_score.view(-1, 2).float(),
                                              next_sentence_label.view(-1).long(), ignore_index=-1)

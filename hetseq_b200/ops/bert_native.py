@@ -398,7 +398,7 @@ class NativeBert(object):
 
     # -- pre-training heads ---------------------------------------------------------------------------
     def pretraining_loss(self, model, input_ids, token_type_ids, attention_mask, masked_lm_labels,
-                         next_sentence_label, checkpoint_activations):
+                         next_sentence_label, checkpoint_activations, mlm_rows=None, mlm_row_labels=None):
         seq, pooled = model.bert(input_ids, token_type_ids, attention_mask, output_all_encoded_layers=False,
                                  checkpoint_activations=checkpoint_activations)
         B, S = input_ids.shape
@@ -407,14 +407,14 @@ class NativeBert(object):
         if model.mlm_all_positions:
             hidden, lab = seq.reshape(B * S, H), labels.contiguous()
         else:
-            # labelled rows only; capacity is data dependent here (eager). Under CUDA graphs the
-            # trainer passes a fixed-capacity index computed on the host.
-            rows = getattr(self, 'mlm_rows', None)
-            if rows is None:
+            # labelled rows only. The task normally supplies a fixed-capacity index computed on the host
+            # (no sync, static shapes); without it the index is derived here with a nonzero().
+            if mlm_rows is not None:
+                rows, lab = mlm_rows.contiguous(), mlm_row_labels.contiguous()
+            else:
                 rows = torch.nonzero(labels != -1, as_tuple=False).squeeze(1).to(torch.int32)
+                lab = labels.index_select(0, rows.long()).contiguous()
             hidden = GatherRowsFn.apply(seq.reshape(B * S, H), rows)
-            lab = labels.index_select(0, rows.long()).contiguous() if getattr(self, 'mlm_labels', None) is None \
-                else self.mlm_labels
         pred = model.cls.predictions
         tr = pred.transform
         t = linear(hidden, tr.dense_act.weight, tr.dense_act.bias, [tr.dense_act.weight], [tr.dense_act.bias], act=ACT_GELU)

@@ -41,8 +41,9 @@ class NativeFlatUpdate(object):
                   'hs_sumsq')
         return self.sumsq_out[0].clone()
 
-    def update(self, mult, skip=None) -> None:
-        """``skip``: 0-dim bool tensor; when true on the device the kernel leaves everything untouched."""
+    def update(self, mult, skip=None, hyper_dev=None) -> None:
+        """``skip``: 0-dim bool tensor; when true on the device the kernel leaves everything untouched.
+        ``hyper_dev``: device [lr, step_factor] overriding the host values (CUDA-graph replays)."""
         opt, buf = self.opt, self.opt.buffer
         skip_i = None if skip is None else skip.to(torch.int32).reshape(1)
         h = opt.hyper
@@ -57,20 +58,20 @@ class NativeFlatUpdate(object):
         args_common = (self._base(buf.flat_grad), master.data_ptr())
         if self.kind == 'adam':
             b1, b2 = h['betas']
-            t = opt.step_count
+            t = opt.step_count + 1      # the update being queued (finish_update() commits the count)
             step_factor = math.sqrt(1 - b2 ** t) / (1 - b1 ** t)
             rc = self.lib.hs_adam_flat(
                 *args_common, opt.state['exp_avg'].data_ptr(), opt.state['exp_avg_sq'].data_ptr(),
                 self._base(buf.flat_param), out_dtype, self.nchunks, CHUNK, self.stride,
                 float(h['lr']), float(b1), float(b2), float(h['eps']), float(h['weight_decay']), float(step_factor),
-                mult_host, lib.ptr(mult_dev), None, lib.ptr(skip_i), lib.stream_ptr())
+                mult_host, lib.ptr(mult_dev), lib.ptr(hyper_dev), lib.ptr(skip_i), lib.stream_ptr())
             lib.check(rc, 'hs_adam_flat')
         else:
             rc = self.lib.hs_adadelta_flat(
                 *args_common, opt.state['square_avg'].data_ptr(), opt.state['acc_delta'].data_ptr(),
                 self._base(buf.flat_param), out_dtype, self.nchunks, CHUNK, self.stride,
                 float(h['lr']), float(h['rho']), float(h['eps']), float(h['weight_decay']),
-                mult_host, lib.ptr(mult_dev), None, lib.ptr(skip_i), lib.stream_ptr())
+                mult_host, lib.ptr(mult_dev), lib.ptr(hyper_dev), lib.ptr(skip_i), lib.stream_ptr())
             lib.check(rc, 'hs_adadelta_flat')
         if opt.sharded:
             opt.dp.all_gather_params(buf)

@@ -24,10 +24,10 @@ SIGNATURES = {
     'hs_ipc_open': [ctypes.c_char_p, ctypes.POINTER(vp)],
     'hs_ipc_close': [vp],
     'hs_ipc_free': [vp],
-    'hs_dp_reduce_scatter': [vp, vp, ci, ci, cl, cl, ci, ci, cu, vp, ci, vp],
-    'hs_dp_norm_exchange': [vp, ci, ci, cu, vp, cf, vp, cf, vp, vp, vp],
-    'hs_dp_adam_allgather': [vp, vp, vp, vp, vp, vp, ci, ci, cl, ci, ci, cf, cf, cf, cf, cf, cf, vp, vp, cu, vp, ci, vp],
-    'hs_dp_wait_params': [vp, ci, ci, cu, vp],
+    'hs_dp_reduce_scatter': [vp, vp, ci, ci, cl, cl, ci, ci, cu, vp, vp, ci, vp],
+    'hs_dp_norm_exchange': [vp, ci, ci, cu, vp, vp, cf, vp, cf, vp, vp, vp],
+    'hs_dp_adam_allgather': [vp, vp, vp, vp, vp, vp, ci, ci, cl, ci, ci, cf, cf, cf, cf, cf, cf, vp, vp, cu, vp, vp, ci, vp],
+    'hs_dp_wait_params': [vp, ci, ci, cu, vp, vp],
     'hs_sumsq_noalloc': [vp, ci, cl, ci, cl, vp, ci, vp],
     'hs_adadelta_flat': [vp, vp, vp, vp, vp, ci, cl, ci, cl, cf, cf, cf, cf, cf, vp, vp, vp, vp],
 }

@@ -90,11 +90,19 @@ class _Optimizer(object):
         self._mult = 1.0          # pending host-side gradient multiplier
         self._mult_dev = None     # pending device-side multiplier (0-dim tensor) if any
         self._skip = None         # 0-dim bool tensor: non-finite gradients -> skip this update
-        self._scale_used = 1.0    # loss scale that was applied to the gradients now in the buffer
+        self._scaled = False      # gradients in the buffer carry the loss scale (divide it out in the update)
         self.scaler: Optional[DynamicLossScaler] = None
         if getattr(args, 'fp16', False):
             self.scaler = DynamicLossScaler(args.fp16_init_scale, args.fp16_scale_factor,
                                             args.fp16_scale_window, args.min_loss_scale)
+        # Device mirrors of the host scalars that change from update to update. Kernels and tensor ops
+        # read these instead of baked-in Python floats, so one captured CUDA graph stays valid:
+        #   scale_t  = [loss scale]           hyper_t = [lr, sqrt(1-b2^t)/(1-b1^t)]
+        self.scale_t = torch.full((1,), self.loss_scale, dtype=torch.float32, device=dev)
+        self.hyper_t = torch.zeros(2, dtype=torch.float32, device=dev)
+        self._host_scalars = torch.zeros(3, dtype=torch.float32)
+        if dev.type == 'cuda':
+            self._host_scalars = self._host_scalars.pin_memory()
         self._native = None
         self._init_native()
 
@@ -138,11 +146,31 @@ class _Optimizer(object):
         return self.scaler.loss_scale if self.scaler is not None else 1.0
 
     # -- gradient handling ----------------------------------------------------------------------
+    def sync_device_scalars(self):
+        """Push lr, the bias-correction factor of the NEXT update and the loss scale to the device: the
+        host values go into a pinned staging buffer, two tiny async copies move them. Runs at the start
+        of every update (zero_grad). When the update is replayed from a CUDA graph the copies are part of
+        the graph and only ``write_host_scalars`` runs on the host before each replay."""
+        self.write_host_scalars()
+        self.hyper_t.copy_(self._host_scalars[:2], non_blocking=True)
+        self.scale_t.copy_(self._host_scalars[2:3], non_blocking=True)
+
+    def write_host_scalars(self):
+        t = self.step_count + 1
+        step_factor = 1.0
+        if 'betas' in self.hyper:
+            b1, b2 = self.hyper['betas']
+            step_factor = math.sqrt(1 - b2 ** t) / (1 - b1 ** t)
+        self._host_scalars[0] = float(self.hyper['lr'])
+        self._host_scalars[1] = step_factor
+        self._host_scalars[2] = self.loss_scale
+
     def backward(self, loss):
-        """loss.backward() (optim.py:55-57), scaled by the current loss scale under --fp16."""
+        """loss.backward() (optim.py:55-57), scaled by the current loss scale under --fp16. The scale is
+        read from device memory (``scale_t``)."""
         if self.scaler is not None:
-            self._scale_used = self.scaler.loss_scale
-            loss = loss * self._scale_used
+            self._scaled = True
+            loss = loss * self.scale_t[0]
         loss.backward()
 
     def multiply_grads(self, c):
@@ -153,10 +181,14 @@ class _Optimizer(object):
             self._mult *= float(c)
 
     def _pending_mult(self):
-        m = self._mult / self._scale_used
-        if self._mult_dev is not None:
-            return self._mult_dev.to(torch.float32) * m
-        return m
+        """Host factor x device factor (clip coefficient, world/sample_size, 1/loss_scale)."""
+        md = self._mult_dev
+        if getattr(self, '_scaled', False):
+            inv = 1.0 / self.scale_t[0]
+            md = inv if md is None else md.to(torch.float32) * inv
+        if md is not None:
+            return md.to(torch.float32) * self._mult
+        return self._mult
 
     def _owned(self, flat: torch.Tensor) -> torch.Tensor:
         """Owned elements of a flat buffer: [num_blocks, CHUNK] strided view, or the buffer itself."""
@@ -180,7 +212,9 @@ class _Optimizer(object):
         if getattr(self.dp, 'fused', False):
             # norm partials were accumulated by the reduce-scatter kernels; one exchange kernel gives
             # every rank the same norm / clip coefficient / overflow flag
-            norm = self.dp.norm_exchange(self._mult / self._scale_used, self._mult_dev, float(max_norm))
+            md = self._pending_mult()
+            norm = self.dp.norm_exchange(1.0 if torch.is_tensor(md) else float(md), md if torch.is_tensor(md) else None,
+                                         float(max_norm))
             self._skip = self.dp.scalars[2] != 0
             self._fused_ready = True
             return norm
@@ -198,53 +232,62 @@ class _Optimizer(object):
 
     def zero_grad(self):
         self.buffer.zero_grad()
+        self.sync_device_scalars()
         self._mult, self._mult_dev, self._skip = 1.0, None, None
         self._fused_ready = False
+        self._scaled = False
 
     # -- update ---------------------------------------------------------------------------------
     def step(self, closure=None):
-        """One fused pass over the owned elements. The kernels take the overflow flag from device
-        memory, so the update is queued first and only then is the flag read back for the loss scaler:
-        under --fp16 a non-finite gradient norm leaves parameters and state untouched, halves the loss
-        scale and raises OverflowError like fairseq, so that Controller.train_step's handler (reference
+        """launch_update() + finish_update(): the reference's ``optimizer.step()``. Under --fp16 a
+        non-finite gradient norm leaves parameters and state untouched, halves the loss scale and raises
+        OverflowError like fairseq, so that Controller.train_step's handler (reference
         controller.py:368-371) finally has a raiser."""
+        self.launch_update()
+        overflow = bool(self._skip.item()) if self.scaler is not None else False
+        self.finish_update(overflow)
+
+    def launch_update(self):
+        """Queue the update on the device; nothing here synchronises or depends on host-side values that
+        change between updates (safe to capture in a CUDA graph). The kernels take the overflow flag
+        from device memory and skip themselves when it is set."""
         fused = getattr(self.dp, 'fused', False)
         if self._skip is None or (fused and not getattr(self, '_fused_ready', False)):
             self.clip_grad_norm(0.0)
-        t = self.step_count + 1
         if fused:
-            b1, b2 = self.hyper['betas']
-            self.dp.adam_allgather(self, math.sqrt(1 - b2 ** t) / (1 - b1 ** t))
+            self.dp.adam_allgather(self, 1.0, hyper_dev=self.hyper_t)
         elif self._native is not None:
-            self.step_count = t
-            self._native.update(self._pending_mult(), self._skip)
-            self.step_count = t - 1
-        overflow = False
+            self._native.update(self._pending_mult(), self._skip if self.scaler is not None else None,
+                                hyper_dev=self.hyper_t)
+        else:
+            # PyTorch path (CPU / --kernels torch): needs the host value of the overflow flag first
+            overflow = bool(self._skip.item()) if self.scaler is not None else False
+            if not overflow:
+                self.step_count += 1
+                mult = self._pending_mult()
+                g = self._owned(self.buffer.flat_grad)
+                out = self._owned(self.buffer.flat_param)
+                g32 = g.float() * mult if (torch.is_tensor(mult) or mult != 1.0) else g.float()
+                self._update_torch(g32)
+                if self.master is not self.buffer.flat_param:
+                    out.copy_(self.master)
+                if self.sharded:
+                    self.dp.all_gather_params(self.buffer)
+                self.step_count -= 1
+
+    def finish_update(self, overflow: bool):
+        """Host bookkeeping once the overflow flag of the queued update is known."""
+        self._mult, self._mult_dev, self._skip = 1.0, None, None
+        self._scaled = False
         if self.scaler is not None:
-            overflow = bool(self._skip.item())
             self.scaler.update(overflow)
             if overflow:
-                self._mult, self._mult_dev, self._skip = 1.0, None, None
                 if self.scaler.loss_scale <= self.scaler.min_loss_scale:
                     raise FloatingPointError(
                         'Minimum loss scale reached ({}). Your loss is probably exploding.'.format(
                             self.scaler.min_loss_scale))
                 raise OverflowError('setting loss scale to: ' + str(self.scaler.loss_scale))
-        self.step_count = t
-        if not fused and self._native is None:
-            mult = self._pending_mult()
-            g = self._owned(self.buffer.flat_grad)
-            out = self._owned(self.buffer.flat_param)
-            if torch.is_tensor(mult):
-                g32 = g.float() * mult
-            else:
-                g32 = g.float() * mult if mult != 1.0 else g.float()
-            self._update_torch(g32)
-            if self.master is not self.buffer.flat_param:
-                out.copy_(self.master)
-            if self.sharded:
-                self.dp.all_gather_params(self.buffer)
-        self._mult, self._mult_dev, self._skip = 1.0, None, None
+        self.step_count += 1
 
     def _update_torch(self, g32: torch.Tensor) -> None:
         raise NotImplementedError

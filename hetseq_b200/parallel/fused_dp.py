@@ -111,7 +111,9 @@ class FusedBackend(AllReduceBackend):
         self.skip = torch.zeros(1, dtype=torch.int32, device=dev)
         self.done_counter = torch.zeros(1, dtype=torch.int32, device=dev)
         self.comm_stream = torch.cuda.Stream(device=dev, priority=-1)
-        self.epoch = 0
+        # the update number lives in device memory and is bumped by a tiny device op per update, so the
+        # very same kernel arguments stay valid when the step is replayed from a CUDA graph
+        self.epoch_t = torch.zeros(1, dtype=torch.int32, device=dev)
         self.rs_blocks = int(getattr(args, 'fused_rs_blocks', 0) or 48)
         torch.cuda.synchronize()
         dist.barrier(group=self.group, device_ids=[dev.index])
@@ -135,7 +137,7 @@ class FusedBackend(AllReduceBackend):
         torch.cuda.synchronize()
 
     def begin_update(self, num_micro_batches: int):
-        self.epoch += 1
+        self.epoch_t.add_(1)
         self._handles = []
 
     def _launch(self, b: int):
@@ -146,7 +148,7 @@ class FusedBackend(AllReduceBackend):
         ev.record()
         self.comm_stream.wait_event(ev)
         lib.check(self.L.hs_dp_reduce_scatter(self.grad_ptrs, self.sig_ptrs, self.rank, self.world_size, s // CHUNK,
-                                              e // CHUNK, CHUNK, b, self.epoch, self.sumsq.data_ptr(), self.rs_blocks,
+                                              e // CHUNK, CHUNK, b, 0, self.epoch_t.data_ptr(), self.sumsq.data_ptr(), self.rs_blocks,
                                               self.comm_stream.cuda_stream), 'hs_dp_reduce_scatter')
 
     def finish_gradients(self, optimizer):
@@ -162,12 +164,13 @@ class FusedBackend(AllReduceBackend):
         0-dim norm tensor; ``self.scalars`` / ``self.skip`` feed the update kernel."""
         md = None if mult_dev is None else mult_dev.to(torch.float32).reshape(1).contiguous()
         self._mult_keepalive = md
-        lib.check(self.L.hs_dp_norm_exchange(self.sig_ptrs, self.rank, self.world_size, self.epoch, self.sumsq.data_ptr(),
+        lib.check(self.L.hs_dp_norm_exchange(self.sig_ptrs, self.rank, self.world_size, 0, self.epoch_t.data_ptr(),
+                                             self.sumsq.data_ptr(),
                                              float(mult_host), lib.ptr(md), float(max_norm), self.scalars.data_ptr(),
                                              self.skip.data_ptr(), lib.stream_ptr()), 'hs_dp_norm_exchange')
         return self.scalars[0]
 
-    def adam_allgather(self, opt, step_factor: float):
+    def adam_allgather(self, opt, step_factor: float, hyper_dev: Optional[torch.Tensor] = None):
         h = opt.hyper
         b1, b2 = h['betas']
         buf = self.buffer
@@ -175,10 +178,10 @@ class FusedBackend(AllReduceBackend):
             buf.flat_grad.data_ptr(), opt.master.data_ptr(), opt.state['exp_avg'].data_ptr(),
             opt.state['exp_avg_sq'].data_ptr(), self.param_ptrs, self.sig_ptrs, self.rank, self.world_size,
             buf.num_blocks, CHUNK, lib.dtype_code(buf.param_dtype), float(h['lr']), float(b1), float(b2), float(h['eps']),
-            float(h['weight_decay']), float(step_factor), self.scalars.data_ptr(), None, self.epoch,
-            self.done_counter.data_ptr(), 0, lib.stream_ptr()), 'hs_dp_adam_allgather')
-        lib.check(self.L.hs_dp_wait_params(self.sig_ptrs, self.rank, self.world_size, self.epoch, lib.stream_ptr()),
-                  'hs_dp_wait_params')
+            float(h['weight_decay']), float(step_factor), self.scalars.data_ptr(), lib.ptr(hyper_dev), 0,
+            self.epoch_t.data_ptr(), self.done_counter.data_ptr(), 0, lib.stream_ptr()), 'hs_dp_adam_allgather')
+        lib.check(self.L.hs_dp_wait_params(self.sig_ptrs, self.rank, self.world_size, 0, self.epoch_t.data_ptr(),
+                                           lib.stream_ptr()), 'hs_dp_wait_params')
 
     # -- sharded-optimizer interface (checkpoint gathering etc.) ---------------------------------------------
     def all_gather_compact(self, compact: torch.Tensor) -> torch.Tensor:

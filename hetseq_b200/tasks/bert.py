@@ -92,10 +92,32 @@ class LanguageModelingTask(Task):
         ntokens = int(mask.sum()) if mask.device.type == 'cpu' else int(input_ids.numel())
         return int(input_ids.shape[0]), ntokens
 
+    def mlm_index(self, masked_lm_labels: torch.Tensor):
+        """Host-side (numpy) flat indices + labels of the labelled positions, padded with -1 to a fixed
+        capacity of ``batch x max predictions per sequence`` (rounded up to 64). Replaces the on-device
+        ``nonzero`` (a sync) and makes the MLM head's shapes static."""
+        lab = masked_lm_labels.reshape(-1).numpy()
+        rows = np.nonzero(lab != -1)[0]
+        B = masked_lm_labels.shape[0]
+        per_seq = int((masked_lm_labels != -1).sum(1).max()) if rows.size else 1
+        self._max_pred_seen = max(getattr(self, '_max_pred_seen', 0), per_seq,
+                                  int(getattr(self.args, 'synthetic_max_predictions', 0) or 0)
+                                  if getattr(self.args, 'synthetic_data', False) else 0)
+        cap = (max(B * self._max_pred_seen, rows.size, 1) + 63) // 64 * 64
+        idx = np.full(cap, -1, dtype=np.int32)
+        idx[:rows.size] = rows
+        row_labels = np.full(cap, -1, dtype=np.int32)
+        row_labels[:rows.size] = lab[rows]
+        return torch.from_numpy(idx), torch.from_numpy(row_labels)
+
     def prepare_sample(self, sample, device):
         """int64 on disk, int32 on the wire: token ids and labels fit in 32 bits and the native
-        kernels consume int32 directly; PyTorch-path modules widen as needed."""
+        kernels consume int32 directly; PyTorch-path modules widen as needed. Appends
+        the host-computed MLM row index (see ``mlm_index``) unless ``--mlm-all-positions``."""
         from hetseq_b200.utils import utils
+        sample = list(sample)
+        if len(sample) == 5 and sample[3].device.type == 'cpu' and not getattr(self.args, 'mlm_all_positions', False):
+            sample += list(self.mlm_index(sample[3]))
         if torch.device(device).type == 'cuda':
             sample = [t.to(torch.int32) if t.dtype == torch.int64 else t for t in sample]
         return utils.move_to_device(sample, device)

@@ -181,7 +181,9 @@ HS_API int hs_attention_bwd(const void* qkv, const float* mask, const void* ctx,
  * Buffers come from hs_ipc_alloc and are mapped into every peer with hs_ipc_open; *_ptrs are HOST arrays
  * of W device pointers indexed by rank (entry [rank] is the local buffer). Ownership is cyclic by chunk:
  * chunk c of the flat buffers belongs to rank c % W. Flags in the signal pads carry `epoch` (the update
- * number, strictly increasing); pads are hs_dp_signal_words() 32-bit words, zero-initialised. */
+ * number, strictly increasing); when `epoch_dev` is non-NULL the kernels read the epoch from that device
+ * word instead (so a captured CUDA graph stays valid across updates). Pads are hs_dp_signal_words()
+ * 32-bit words, zero-initialised. */
 HS_API int hs_ipc_alloc(size_t bytes, void** ptr, unsigned char* handle64);
 HS_API int hs_ipc_open(const unsigned char* handle64, void** ptr);
 HS_API int hs_ipc_close(void* ptr);
@@ -192,11 +194,11 @@ HS_API int hs_dp_signal_words(int W, int max_buckets);
  * the squared sum into *sumsq_accum. Launch on a side stream as soon as the bucket's gradients are final. */
 HS_API int hs_dp_reduce_scatter(void* const* grad_ptrs, void* const* sig_ptrs, int rank, int W,
                                 long long chunk_begin, long long chunk_end, int chunk, int slot, unsigned epoch,
-                                float* sumsq_accum, int nblocks, hs_stream_t stream);
+                                const unsigned* epoch_dev, float* sumsq_accum, int nblocks, hs_stream_t stream);
 /* All ranks exchange their norm partial through the pads and derive identical
  * out4 = [grad_norm, multiplier * clip coefficient, overflow flag, global sum of squares]; *skip_out = flag. */
-HS_API int hs_dp_norm_exchange(void* const* sig_ptrs, int rank, int W, unsigned epoch, float* sumsq_accum,
-                               float mult_host, const float* mult_dev, float max_norm, float* out4, int* skip_out,
+HS_API int hs_dp_norm_exchange(void* const* sig_ptrs, int rank, int W, unsigned epoch, const unsigned* epoch_dev,
+                               float* sumsq_accum, float mult_host, const float* mult_dev, float max_norm, float* out4, int* skip_out,
                                hs_stream_t stream);
 /* Adam (math of optim.py:162-231) on the owned chunks; the updated 16-bit parameters are stored into all W
  * parameter buffers (the all-gather). scalars = out4 of hs_dp_norm_exchange. */
@@ -204,9 +206,11 @@ HS_API int hs_dp_adam_allgather(const float* grad, float* master, float* exp_avg
                                 void* const* param_ptrs, void* const* sig_ptrs, int rank, int W, long long nblocks,
                                 int chunk, int out_dtype, float lr, float beta1, float beta2, float eps,
                                 float weight_decay, float step_factor, const float* scalars, const float* hyper_dev,
-                                unsigned epoch, unsigned int* done_counter, int grid_blocks, hs_stream_t stream);
+                                unsigned epoch, const unsigned* epoch_dev, unsigned int* done_counter, int grid_blocks,
+                                hs_stream_t stream);
 /* Returns (on the stream) once every rank's parameter stores of update `epoch` have landed locally. */
-HS_API int hs_dp_wait_params(void* const* sig_ptrs, int rank, int W, unsigned epoch, hs_stream_t stream);
+HS_API int hs_dp_wait_params(void* const* sig_ptrs, int rank, int W, unsigned epoch, const unsigned* epoch_dev,
+                             hs_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -55,7 +55,10 @@ def test_native_loss_and_grads_match_torch(tmp_path, flag):
     ctl.get_model().train()
     ctl.zero_grad()
     loss = ctl.get_model()(*dev)
-    loss.backward()
+    # fp16 needs a loss scale like in real training (the attention gradients are ~1e-6 and would sit in
+    # fp16's subnormal range otherwise); compare unscaled
+    scale = 4096.0 if flag == '--fp16' else 1.0
+    (loss * scale).backward()
     ref.train()
     ref_loss = ref(*[t.cuda() for t in sample])
     ref_loss.backward()
@@ -63,7 +66,7 @@ def test_native_loss_and_grads_match_torch(tmp_path, flag):
     named = dict(ref.named_parameters())
     errs = {}
     for name, p in ctl.get_model().named_parameters():
-        g, rg = p.main_grad.float(), named[name].grad
+        g, rg = p.main_grad.float() / scale, named[name].grad
         # relative error in the Frobenius norm: 16-bit activations vs the fp32 oracle
         if 'key.bias' in name:
             continue   # mathematically zero (softmax is shift invariant per row): only noise to compare
@@ -87,3 +90,32 @@ def test_native_training_reduces_loss(tmp_path):
 def test_smoke_entry():
     import __graft_entry__ as g
     g.smoke()
+
+
+def test_cuda_graph_step_matches_eager(tmp_path):
+    """--cuda-graph replays the captured update; with dropout off it must track the eager run."""
+    import copy
+    from hetseq_b200.data.bert_dataset import SyntheticBertData
+    ds = SyntheticBertData(64, 128, 10, 2000, seed=5)
+    batches = [ds.fetch_rows(list(range(i * 8, i * 8 + 8))) for i in range(8)]
+    results = {}
+    for mode in ('eager', 'graph'):
+        d = os.path.join(str(tmp_path), mode)
+        os.makedirs(d)
+        ctl, task = _build(d, '--fp16', 'native', seed=0)
+        ctl.args.cuda_graph = (mode == 'graph')
+        ctl._graph_enabled = (mode == 'graph')
+        losses = []
+        for b in batches:
+            out = ctl.train_step([b])
+            losses.append(None if out is None else out['loss'])
+        if mode == 'graph':
+            assert ctl._graph is not None, 'the step was never captured'
+        results[mode] = (losses, ctl.buffer.flat_param.detach().float().clone(), ctl.get_num_updates())
+    (le, pe, ne), (lg, pg, ng) = results['eager'], results['graph']
+    assert ne == ng
+    for a, b in zip(le, lg):
+        assert (a is None) == (b is None)
+        if a is not None:
+            assert abs(a - b) < 2e-2, (le, lg)
+    assert (pe - pg).abs().max().item() < 3e-3
