@@ -7,8 +7,10 @@
 //   warp 1   MMA issuer:   one elected thread issues tcgen05.mma (128 x BN x 16) per k-step, commits
 //                          ring slots back to the producer and finished accumulators to the epilogue
 //   warps 2-9 epilogue:    tcgen05.ld the accumulator (double-buffered in TMEM, so the next tile's
-//                          MMAs overlap this tile's epilogue), apply bias / GELU / tanh / dGELU /
-//                          accumulate, convert and store
+//                          MMAs overlap this tile's epilogue), apply bias / GELU / tanh / dGELU, convert,
+//                          stage 32-row x 128-byte boxes in swizzled smem and hand them to the TMA:
+//                          plain bulk store, or bulk REDUCE-ADD (fp32) when accumulating -- which is also
+//                          what makes split-K work for the wgrad shapes with few output tiles
 // Operands may be K-major or MN-major in global memory (both are expressed through the TMA box
 // shape and the UMMA shared-memory descriptor), so forward, dgrad and wgrad all run without any
 // transpose pass:  forward X*W^T = (K,K);  dgrad dY*W = (K,MN);  wgrad dY^T*X = (MN,MN).
@@ -20,6 +22,7 @@
 #include "host.h"
 #include "../include/hetseq_b200.h"
 
+#include <cstring>
 #include <mutex>
 
 namespace hs {
@@ -44,14 +47,18 @@ struct GemmParams {
   int act, accumulate;
   float alpha;
   const float* alpha_dev;
-  int vec_ok;  // C/aux rows are 16-byte aligned -> vector loads/stores allowed
+  int vec_ok;    // C/aux rows are 16-byte aligned -> vector loads/stores allowed
+  int tma_store; // epilogue goes through smem + TMA (needs vec_ok); else per-thread global stores
+  int split_k;   // >1: several work items per output tile, each reduce-adds its K range
+  int kb_per_split;
 };
 
 template <int BN> struct GemmCfg {
   static constexpr int STAGES = (BN == 256) ? 4 : 6;
   static constexpr int B_STAGE_BYTES = BN * 128;
   static constexpr int TMEM_COLS = 2 * BN;
-  static constexpr int SMEM_BYTES = STAGES * (A_STAGE_BYTES + B_STAGE_BYTES) + 2 * BN * 4 /*bias*/ +
+  static constexpr int STAGING_BYTES = EPI_WARPS * 4096;  // one 32-row x 128-byte box per epilogue warp
+  static constexpr int SMEM_BYTES = STAGES * (A_STAGE_BYTES + B_STAGE_BYTES) + STAGING_BYTES +
                                     (2 * STAGES + 4) * 8 /*mbarriers*/ + 16 /*tmem slot*/ + 1024 /*align*/;
 };
 
@@ -113,6 +120,7 @@ __device__ __forceinline__ void store_row32(T* __restrict__ p, int n0, int N, bo
 template <int BN, typename InT, typename OutT>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmAux,
                     const GemmParams p) {
   using Cfg = GemmCfg<BN>;
   constexpr int STAGES = Cfg::STAGES;
@@ -122,8 +130,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sA = smem;
   uint8_t* sB = smem + STAGES * A_STAGE_BYTES;
-  float* sBias = reinterpret_cast<float*>(sB + STAGES * B_STAGE_BYTES);
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(sBias + 2 * BN);
+  uint8_t* sStage = sB + STAGES * B_STAGE_BYTES;   // 1024-aligned: every stage size is a multiple of 1024
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(sStage + Cfg::STAGING_BYTES);
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tfull_bar = empty_bar + STAGES;
   uint64_t* tempty_bar = tfull_bar + 2;
@@ -132,10 +140,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int num_tiles = p.tiles_m * p.tiles_n;
+  const int num_work = num_tiles * p.split_k;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
+    if (p.tma_store) tma_prefetch_desc(&tmC);
   }
   if (warp == 1) {
     if (lane == 0) {
@@ -162,9 +172,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int work = blockIdx.x; work < num_work; work += gridDim.x) {
+        const int tile = work % num_tiles, ks = work / num_tiles;
         const int tm = tile % p.tiles_m, tn = tile / p.tiles_m;
-        for (int kb = 0; kb < p.num_kb; ++kb) {
+        const int kb0 = ks * p.kb_per_split, kb1 = min(p.num_kb, kb0 + p.kb_per_split);
+        for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           mbar_expect_tx(&full_bar[stage], A_STAGE_BYTES + B_STAGE_BYTES);
           uint8_t* a_dst = sA + stage * A_STAGE_BYTES;
@@ -193,11 +205,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     uint32_t phase = 0;
     int as = 0;
     uint32_t aphase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    for (int work = blockIdx.x; work < num_work; work += gridDim.x) {
+      const int ks = work / num_tiles;
+      const int kb0 = ks * p.kb_per_split, kb1 = min(p.num_kb, kb0 + p.kb_per_split);
       mbar_wait(&tempty_bar[as], aphase ^ 1);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + as * BN;
-      for (int kb = 0; kb < p.num_kb; ++kb) {
+      for (int kb = kb0; kb < kb1; ++kb) {
         mbar_wait(&full_bar[stage], phase);
         tc_fence_after();
         if (elect_one_sync()) {
@@ -208,10 +222,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
             umma_f16(d_tmem, adesc + ((k * p.a_kadv) >> 4), bdesc + ((k * p.b_kadv) >> 4), p.idesc,
-                     (kb | k) != 0 ? 1u : 0u);
+                     (kb != kb0 || k != 0) ? 1u : 0u);
           }
-          umma_commit(&empty_bar[stage]);                        // ring slot free once these MMAs retire
-          if (kb == p.num_kb - 1) umma_commit(&tfull_bar[as]);   // accumulator complete
+          umma_commit(&empty_bar[stage]);                  // ring slot free once these MMAs retire
+          if (kb == kb1 - 1) umma_commit(&tfull_bar[as]);   // accumulator complete
         }
         __syncwarp();
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -220,67 +234,152 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
   } else {
     // ===================== epilogue (warps 2..9) =====================
-    const int q = warp & 3;  // TMEM lane quarter this warp may access
+    const int q = warp & 3;            // TMEM lane quarter this warp may access
     const int half = (warp - 2) >> 2;  // which half of the tile's columns this warp drains
-    const int et = threadIdx.x - 64;
     const InT* bias = reinterpret_cast<const InT*>(p.bias);
     OutT* C = reinterpret_cast<OutT*>(p.C);
     const bool vec = p.vec_ok != 0;
+    const bool tma = p.tma_store != 0;
     const float alpha = p.alpha * (p.alpha_dev != nullptr ? *p.alpha_dev : 1.0f);
+    constexpr int CW = (sizeof(OutT) == 2) ? 64 : 32;   // columns per 128-byte staging row
+    uint8_t* stg = sStage + (warp - 2) * 4096;
     int as = 0;
     uint32_t aphase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    for (int work = blockIdx.x; work < num_work; work += gridDim.x) {
+      const int tile = work % num_tiles, ks = work / num_tiles;
       const int tm = tile % p.tiles_m, tn = tile / p.tiles_m;
       const int n_base = tn * BN;
-      float* sb = sBias + as * BN;
-      if (bias != nullptr) {
-        for (int i = et; i < BN; i += EPI_WARPS * 32) sb[i] = (n_base + i < p.N) ? Cvt<InT>::to_f(bias[n_base + i]) : 0.0f;
-      }
-      asm volatile("bar.sync 1, %0;" ::"n"(EPI_WARPS * 32) : "memory");
       mbar_wait(&tfull_bar[as], aphase);
+      __syncwarp();
       tc_fence_after();
-      const int m = tm * BM + q * 32 + lane;
+      const int m0 = tm * BM + q * 32;
+      const int m = m0 + lane;
       const bool row_ok = m < p.M;
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
+      const bool add_bias = bias != nullptr && ks == 0;
 #pragma unroll 1
-      for (int cc = 0; cc < BN / 64; ++cc) {
-        const int c = half * (BN / 64) + cc;
-        const int n0 = n_base + c * 32;
+      for (int cc = 0; cc < (BN / 2) / CW; ++cc) {
+        const int c0 = half * (BN / 2) + cc * CW;
+        const int n0 = n_base + c0;
         if (n0 >= p.N) break;  // warp-uniform
-        uint32_t r[32];
-        tmem_ld_32x32(t_row + c * 32, r);
-        tmem_ld_wait();
-        float v[32];
+        float v[CW];
 #pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]) * alpha;
-        if (bias != nullptr) {
+        for (int sub = 0; sub < CW / 32; ++sub) {
+          uint32_t r[32];
+          tmem_ld_32x32(t_row + c0 + sub * 32, r);
+          tmem_ld_wait();
 #pragma unroll
-          for (int i = 0; i < 32; ++i) v[i] += sb[c * 32 + i];
+          for (int i = 0; i < 32; ++i) v[sub * 32 + i] = __uint_as_float(r[i]) * alpha;
         }
-        if (row_ok) {
-          if (p.act == HS_ACT_GELU) {
-            if (p.aux_out != nullptr) {
-              store_row32<InT>(reinterpret_cast<InT*>(p.aux_out) + static_cast<size_t>(m) * p.ldaux, n0, p.N, vec, v);
+        if (add_bias) {
+          if (n0 + CW <= p.N) {
+#pragma unroll
+            for (int j = 0; j < CW / 8; ++j) {
+              const uint4 u = *reinterpret_cast<const uint4*>(bias + n0 + j * 8);
+              const float2 f0 = Cvt<InT>::unpack2(u.x), f1 = Cvt<InT>::unpack2(u.y), f2 = Cvt<InT>::unpack2(u.z),
+                           f3 = Cvt<InT>::unpack2(u.w);
+              v[j * 8 + 0] += f0.x; v[j * 8 + 1] += f0.y; v[j * 8 + 2] += f1.x; v[j * 8 + 3] += f1.y;
+              v[j * 8 + 4] += f2.x; v[j * 8 + 5] += f2.y; v[j * 8 + 6] += f3.x; v[j * 8 + 7] += f3.y;
             }
+          } else {
 #pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] = gelu_ref(v[i]);
-          } else if (p.act == HS_ACT_TANH) {
-#pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] = tanhf(v[i]);
-          } else if (p.act == HS_ACT_DGELU_MUL) {
-            float x[32];
-            load_row32<InT>(reinterpret_cast<const InT*>(p.aux_in) + static_cast<size_t>(m) * p.ldaux, n0, p.N, vec, x);
-#pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] *= gelu_grad_ref(x[i]);
+            for (int i = 0; i < CW; ++i)
+              if (n0 + i < p.N) v[i] += Cvt<InT>::to_f(bias[n0 + i]);
           }
+        }
+        // ---- activation (pre-activation goes out first when requested)
+        if (p.act == HS_ACT_GELU) {
+          if (p.aux_out != nullptr) {
+            if constexpr (sizeof(OutT) == 2) {
+              if (tma) {
+                if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+                __syncwarp();
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                  uint4 u;
+                  u.x = Cvt<InT>::pack2(v[j * 8 + 0], v[j * 8 + 1]); u.y = Cvt<InT>::pack2(v[j * 8 + 2], v[j * 8 + 3]);
+                  u.z = Cvt<InT>::pack2(v[j * 8 + 4], v[j * 8 + 5]); u.w = Cvt<InT>::pack2(v[j * 8 + 6], v[j * 8 + 7]);
+                  *reinterpret_cast<uint4*>(stg + lane * 128 + ((j ^ (lane & 7)) << 4)) = u;
+                }
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0) {
+                  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                               ::"l"(reinterpret_cast<uint64_t>(&tmAux)), "r"(smem_u32(stg)), "r"(n0), "r"(m0) : "memory");
+                  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                }
+              } else if (row_ok) {
+#pragma unroll
+                for (int sub = 0; sub < CW / 32; ++sub) {
+                  float t32[32];
+#pragma unroll
+                  for (int i = 0; i < 32; ++i) t32[i] = v[sub * 32 + i];
+                  store_row32<InT>(reinterpret_cast<InT*>(p.aux_out) + static_cast<size_t>(m) * p.ldaux, n0 + sub * 32, p.N, vec, t32);
+                }
+              }
+            }
+          }
+#pragma unroll
+          for (int i = 0; i < CW; ++i) v[i] = gelu_ref(v[i]);
+        } else if (p.act == HS_ACT_TANH) {
+#pragma unroll
+          for (int i = 0; i < CW; ++i) v[i] = tanhf(v[i]);
+        } else if (p.act == HS_ACT_DGELU_MUL) {
+          if (row_ok) {
+#pragma unroll
+            for (int sub = 0; sub < CW / 32; ++sub) {
+              float x[32];
+              load_row32<InT>(reinterpret_cast<const InT*>(p.aux_in) + static_cast<size_t>(m) * p.ldaux, n0 + sub * 32, p.N, vec, x);
+#pragma unroll
+              for (int i = 0; i < 32; ++i) v[sub * 32 + i] *= gelu_grad_ref(x[i]);
+            }
+          }
+        }
+        // ---- output
+        if (tma) {
+          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // staging box is free again
+          __syncwarp();
+          if constexpr (sizeof(OutT) == 2) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              uint4 u;
+              u.x = Cvt<OutT>::pack2(v[j * 8 + 0], v[j * 8 + 1]); u.y = Cvt<OutT>::pack2(v[j * 8 + 2], v[j * 8 + 3]);
+              u.z = Cvt<OutT>::pack2(v[j * 8 + 4], v[j * 8 + 5]); u.w = Cvt<OutT>::pack2(v[j * 8 + 6], v[j * 8 + 7]);
+              *reinterpret_cast<uint4*>(stg + lane * 128 + ((j ^ (lane & 7)) << 4)) = u;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              *reinterpret_cast<float4*>(stg + lane * 128 + ((j ^ (lane & 7)) << 4)) =
+                  make_float4(v[j * 4 + 0], v[j * 4 + 1], v[j * 4 + 2], v[j * 4 + 3]);
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            if (p.accumulate) {
+              asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];"
+                           ::"l"(reinterpret_cast<uint64_t>(&tmC)), "r"(smem_u32(stg)), "r"(n0), "r"(m0) : "memory");
+            } else {
+              asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                           ::"l"(reinterpret_cast<uint64_t>(&tmC)), "r"(smem_u32(stg)), "r"(n0), "r"(m0) : "memory");
+            }
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          }
+        } else if (row_ok) {
           OutT* crow = C + static_cast<size_t>(m) * p.ldc;
-          if (p.accumulate) {
-            float o[32];
-            load_row32<OutT>(crow, n0, p.N, vec, o);
 #pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] += o[i];
+          for (int sub = 0; sub < CW / 32; ++sub) {
+            float t32[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) t32[i] = v[sub * 32 + i];
+            if (p.accumulate) {
+              float o[32];
+              load_row32<OutT>(crow, n0 + sub * 32, p.N, vec, o);
+#pragma unroll
+              for (int i = 0; i < 32; ++i) t32[i] += o[i];
+            }
+            store_row32<OutT>(crow, n0 + sub * 32, p.N, vec, t32);
           }
-          store_row32<OutT>(crow, n0, p.N, vec, v);
         }
       }
       tc_fence_before();
@@ -288,6 +387,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       if (lane == 0) mbar_arrive(&tempty_bar[as]);
       if (++as == 2) { as = 0; aphase ^= 1; }
     }
+    // every bulk store of this warp must have completed before the CTA (and its smem) goes away
+    if (tma && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   }
 
   tc_fence_before();
@@ -317,8 +418,16 @@ static PFN_encodeTiled get_encode_fn() {
   return fn;
 }
 
+static int make_tmap_2d(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t ld,
+                        uint32_t box_inner, uint32_t box_outer, int elem_bytes);
+
 int make_tmap_2d_16b(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t ld,
                      uint32_t box_inner, uint32_t box_outer) {
+  return make_tmap_2d(out, base, inner, outer, ld, box_inner, box_outer, 2);
+}
+
+static int make_tmap_2d(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t ld,
+                        uint32_t box_inner, uint32_t box_outer, int elem_bytes) {
   // cuTensorMapEncodeTiled is a driver-API call: it needs the primary context to be current on THIS
   // thread. A thread that has only ever inherited the default device (e.g. PyTorch's autograd worker
   // on device 0) has no context bound until its first context-requiring runtime call -- force that.
@@ -333,10 +442,11 @@ int make_tmap_2d_16b(CUtensorMap* out, const void* base, uint64_t inner, uint64_
     return 1;
   }
   cuuint64_t dims[2] = {inner, outer};
-  cuuint64_t strides[1] = {ld * 2};
+  cuuint64_t strides[1] = {ld * static_cast<uint64_t>(elem_bytes)};
   cuuint32_t box[2] = {box_inner, box_outer};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+  CUresult r = enc(out, elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_UINT16, 2,
+                   const_cast<void*>(base), dims, strides, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
@@ -387,10 +497,35 @@ static int launch_gemm(const hs_gemm_args& a, cudaStream_t stream) {
   if (a.aux_out) vec = vec && (reinterpret_cast<uintptr_t>(a.aux_out) % 16 == 0) && ((a.ldaux * 2) % 16 == 0);
   if (a.aux_in) vec = vec && (reinterpret_cast<uintptr_t>(a.aux_in) % 16 == 0) && ((a.ldaux * 2) % 16 == 0);
   p.vec_ok = vec ? 1 : 0;
+  // 16-bit read-modify-write accumulation has no TMA reduce type here: it keeps the per-thread path
+  p.tma_store = (vec && !(a.accumulate && sizeof(OutT) == 2)) ? 1 : 0;
 
   const int tiles = p.tiles_m * p.tiles_n;
-  const int grid = tiles < num_sms() ? tiles : num_sms();
-  kern<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, p);
+  const int sms = num_sms();
+  // split-K: only with the reduce-add epilogue (C already holds a valid partial sum) and no per-column work
+  p.split_k = 1;
+  if (p.tma_store && a.accumulate && a.bias == nullptr && a.act == HS_ACT_NONE && tiles < sms) {
+    double best = 1e30;
+    for (int s = 1; s <= 8 && s * 4 <= p.num_kb; ++s) {
+      const int items = tiles * s;
+      const int waves = (items + sms - 1) / sms;
+      const double cost = waves * ((p.num_kb + s - 1) / s + 6.0);   // +6 k-blocks ~ prologue + epilogue of an item
+      if (cost < best - 1e-9) { best = cost; p.split_k = s; }
+    }
+  }
+  p.kb_per_split = (p.num_kb + p.split_k - 1) / p.split_k;
+
+  CUtensorMap tmC, tmAux;
+  memset(&tmC, 0, sizeof(tmC));
+  memset(&tmAux, 0, sizeof(tmAux));
+  if (p.tma_store) {
+    constexpr int CW = sizeof(OutT) == 2 ? 64 : 32;
+    if (make_tmap_2d(&tmC, a.C, a.N, a.M, a.ldc, CW, 32, sizeof(OutT))) return 1;
+    if (a.aux_out != nullptr && make_tmap_2d(&tmAux, a.aux_out, a.N, a.M, a.ldaux, 64, 32, 2)) return 1;
+  }
+  const int work = tiles * p.split_k;
+  const int grid = work < sms ? work : sms;
+  kern<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, tmC, tmAux, p);
   return post_launch("gemm_tcgen05_kernel");
 }
 
