@@ -99,7 +99,7 @@ def batch_offsets_numpy(sizes: np.ndarray, max_tokens: int, max_sentences: int, 
             mod_len = max(bsz_mult * (length // bsz_mult), length % bsz_mult)
             start += mod_len
             offsets.append(start)
-            sample_len = int(sizes[start:i].max()) if i > start else 0
+            sample_len = int(sizes[start:i + 1].max())
     if n - start > 0:
         offsets.append(n)
     return np.asarray(offsets, dtype=np.int64)

@@ -33,11 +33,10 @@ HS_EXPORT int64_t hs_batch_by_size(const int64_t* sizes, int64_t n, int64_t max_
       const int64_t mod_len = std::max(bsz_mult * (len / bsz_mult), len % bsz_mult);
       start += mod_len;
       out_offsets[++nb] = start;
-      // carried samples [start, i) plus the new one determine the running max. The reference takes
-      // the max over the carried samples only and then appends idx (data_utils_fast.pyx:56-58), so
-      // the new sample's size re-enters at the next iteration; reproduce that exactly.
+      // the running max restarts over the carried samples [start, i) and the sample being added
+      // (data_utils_fast.pyx:40-41,56-57: its length was appended to sample_lens before the flush)
       sample_len = 0;
-      for (int64_t j = start; j < i; ++j) sample_len = std::max(sample_len, sizes[j]);
+      for (int64_t j = start; j <= i; ++j) sample_len = std::max(sample_len, sizes[j]);
     }
   }
   if (n - start > 0) out_offsets[++nb] = n;

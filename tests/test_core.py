@@ -1,0 +1,229 @@
+"""Flags, meters/log line, LR schedule, optimizers, checkpoints/resume, all_gather_list (single process)."""
+import argparse
+import math
+import os
+
+import pytest
+import torch
+
+from hetseq_b200 import options, registry
+from hetseq_b200.optim import Adam, Adadelta, _Adam, _Adadelta, PolynomialDecayScheduler
+from hetseq_b200.utils import checkpoint_utils, progress_bar, utils
+from hetseq_b200.utils.meters import AverageMeter, StopwatchMeter, TimeMeter
+
+
+def test_reference_flags_and_defaults(tmp_path):
+    a = options.parse_cli(['--task', 'mnist', '--optimizer', 'adadelta', '--data', 'x', '--max-sentences', '8'])
+    assert (a.task, a.optimizer, a.lr_scheduler) == ('mnist', 'adadelta', 'PolynomialDecayScheduler')
+    assert a.seed == 19940802 and a.clip_norm == 25 and a.lr == [0.25] and a.update_freq == [1]
+    assert a.bucket_cap_mb == 25 and a.distributed_gpus == 4 and a.distributed_backend == 'nccl'
+    assert a.restore_file == 'checkpoint_last.pt' and a.save_dir == 'checkpoints' and a.total_num_update == 1000000
+    assert a.adadelta_rho == 0.9 and a.dadelta_weight_decay == 0 and a.max_sentences_valid == 8
+    b = options.parse_cli(['--task', 'bert', '--config_file', 'c.json', '--lr', '0.1,0.01', '--update-freq', '[2, 4]',
+                           '--lr_scheduler', 'PolynomialDecayScheduler', '--adam-betas', '(0.9, 0.98)', '--fp16',
+                           '--max-tokens', '4096', '--local_rank', '3', '--me', '5', '--wd', '0.01'])
+    assert b.lr == [0.1, 0.01] and b.update_freq == [2, 4] and b.device_id == 3 and b.max_epoch == 5 and b.fp16
+    assert b.weight_decay == 0.01 and b.max_pred_length == 512 and b.num_file == 0
+    with pytest.raises(SystemExit):
+        options.parse_cli(['--task', 'mnist', '--use-bmuf', '--max-sentences', '1'])      # dead flag of the reference
+    with pytest.raises(SystemExit):
+        options.parse_cli(['--task', 'mnist', '--fp16', '--bf16', '--max-sentences', '1'])
+    with pytest.raises(argparse.ArgumentTypeError):
+        options.eval_str_list('__import__("os").system("true")')                          # no eval()
+    assert options.eval_str_list('3', int) == [3] and options.eval_bool('True') and not options.eval_bool(None)
+
+
+def test_registry_extension():
+    from hetseq_b200.registry import register_task, lookup
+    from hetseq_b200.tasks import Task
+
+    @register_task('unit_test_task')
+    class T(Task):
+        pass
+    assert lookup('task', 'unit_test_task') is T
+    with pytest.raises(ValueError):
+        lookup('optimizer', 'nope')
+    del registry.TASKS['unit_test_task']
+
+
+def test_meters_and_log_line(capsys):
+    m = AverageMeter(); m.update(2, 3); m.update(4)
+    assert m.avg == 2.5 and m.count == 4
+    s = StopwatchMeter(); s.start(); s.stop(); assert s.n == 1 and s.sum >= 0
+    assert progress_bar.format_stat(m) == '2.500' and progress_bar.format_stat(1.00996) == '1.00996'
+    t = TimeMeter(); t.update(5); assert t.avg > 0
+    args = argparse.Namespace(log_format='simple', no_progress_bar=True, log_interval=1, log_file=None)
+    bar = progress_bar.build_progress_bar(args, [10, 11, 12, 13], epoch=1)
+    for i, _ in enumerate(bar):
+        bar.log({'loss': m, 'num_updates': i + 1, 'lr': 0.5})
+    out = capsys.readouterr().out.splitlines()
+    assert out[0] == '| epoch 001:      1 / 4 loss=2.500, num_updates=2, lr=0.5'
+    args.log_format = 'json'
+    bar = progress_bar.build_progress_bar(args, [1, 2], epoch=2)
+    for _ in bar:
+        bar.log({'loss': m})
+    assert '"loss": 2.5' in capsys.readouterr().out
+    assert utils.get_perplexity(3.0) == 8.0 and utils.get_perplexity(1e9) == float('inf')
+
+
+def _args(**kw):
+    a = options.make_args('mnist', kw.pop('optimizer', 'adam'), argv=kw.pop('argv', []))
+    for k, v in kw.items():
+        setattr(a, k, v)
+    return a
+
+
+def test_polynomial_decay_schedule_curve():
+    a = _args(lr=[1.0, 0.5], warmup_updates=4, total_num_update=20, end_learning_rate=0.1, power=2.0)
+    opt = _Adam(a, [torch.nn.Parameter(torch.zeros(3))])
+    sch = PolynomialDecayScheduler(a, opt)
+    assert opt.get_lr() == 0.25                                   # warmup_factor * lr at construction
+    assert sch.step_update(2) == 0.5 and sch.step_update(4) == 1.0
+    expect = (1.0 - 0.1) * (1 - (12 - 4) / (20 - 4)) ** 2 + 0.1
+    assert abs(sch.step_update(12) - expect) < 1e-12
+    assert sch.step_update(20) == 0.1 and sch.step_update(99) == 0.1
+    assert sch.step(1) == 0.5                                      # epoch-indexed --lr list
+    a.force_anneal = 1
+    sch.step_update(12); cur = opt.get_lr()
+    assert sch.step(3) == cur                                      # past force_anneal: keep the current lr
+    sch.step(0, val_loss=2.0); sch.step(0, val_loss=3.0)
+    assert sch.state_dict() == {'best': 2.0}
+
+
+@pytest.mark.parametrize('kind', ['adam', 'adadelta'])
+def test_flat_optimizer_matches_per_tensor_reference(kind):
+    torch.manual_seed(0)
+    shapes = [(7, 5), (13,), (3, 3, 2)]
+    ref_p = [torch.nn.Parameter(torch.randn(s)) for s in shapes]
+    flat_p = [torch.nn.Parameter(p.detach().clone()) for p in ref_p]
+    a = _args(optimizer=kind, lr=[0.05], argv=(['--weight-decay', '0.1'] if kind == 'adam' else []))
+    opt = (_Adam if kind == 'adam' else _Adadelta)(a, flat_p)
+    ref = Adam(ref_p, lr=0.05, weight_decay=0.1) if kind == 'adam' else Adadelta(ref_p, lr=0.05)
+    for step in range(4):
+        opt.zero_grad()
+        grads = [torch.randn(s) for s in shapes]
+        c = 0.3
+        total = math.sqrt(sum(float((g * c).pow(2).sum()) for g in grads))
+        clip = 1.5
+        coef = min(1.0, clip / (total + 1e-6))
+        for p, q, g in zip(ref_p, flat_p, grads):
+            p.grad = g * c * coef
+            q.grad.copy_(g)                      # fp32 params: .grad IS the flat main-grad view
+        opt.multiply_grads(c)
+        gn = opt.clip_grad_norm(clip)
+        assert abs(float(gn) - total) < 1e-5 * total
+        opt.step(); ref.step()
+    for p, q in zip(ref_p, flat_p):
+        torch.testing.assert_close(q.data, p.data, rtol=1e-6, atol=1e-7)
+    # state dict has the per-parameter layout of a plain torch optimizer and round-trips
+    sd = opt.state_dict()
+    names = ('exp_avg', 'exp_avg_sq') if kind == 'adam' else ('square_avg', 'acc_delta')
+    assert sorted(sd['state']) == [0, 1, 2] and sd['state'][1]['step'] == 4
+    for i, p in enumerate(ref_p):
+        torch.testing.assert_close(sd['state'][i][names[0]], ref.state[p][names[0]], rtol=1e-6, atol=1e-8)
+    opt2 = (_Adam if kind == 'adam' else _Adadelta)(a, [torch.nn.Parameter(p.detach().clone()) for p in flat_p])
+    opt2.load_state_dict(sd, {'lr': 0.123})
+    assert opt2.get_lr() == 0.123 and opt2.step_count == 4
+    torch.testing.assert_close(opt2.state[names[1]], opt.state[names[1]])
+
+
+def test_fp16_overflow_skips_update_and_halves_scale():
+    a = _args(lr=[0.1], fp16=True, fp16_init_scale=8.0, fp16_scale_window=2)
+    p = torch.nn.Parameter(torch.ones(4).half())
+    opt = _Adam(a, [p])
+    opt.zero_grad()
+    (p.float().sum() * 1.0).backward()          # dummy: produce a grad through the hook path
+    p.main_grad.fill_(float('inf'))
+    opt._scaled = True
+    with pytest.raises(OverflowError):
+        opt.step()
+    assert opt.loss_scale == 4.0 and opt.step_count == 0 and torch.equal(p.data, torch.ones(4).half())
+    for _ in range(2):                           # two clean updates -> the scale grows back
+        opt.zero_grad()
+        opt.backward(p.float().sum())
+        opt.step()
+    assert opt.loss_scale == 8.0 and opt.step_count == 2 and float(p.data[0]) < 1.0
+
+
+def _tiny_mnist_controller(tmp_path, **kw):
+    from hetseq_b200.controller import Controller
+    from hetseq_b200.data.mnist_dataset import make_synthetic_mnist
+    data = str(tmp_path / 'data')
+    if not os.path.exists(data):
+        make_synthetic_mnist(data, 64, 16)
+    argv = ['--data', data, '--cpu', '--max-sentences', '16', '--lr', '0.5', '--save-dir', str(tmp_path / 'ckpt'),
+            '--distributed-world-size', '1', '--log-format', 'none']
+    a = options.make_args('mnist', 'adadelta', argv=argv, **kw)
+    torch.manual_seed(0)
+    task = registry.lookup('task', 'mnist').setup_task(a)
+    ctl = Controller(a, task, task.build_model(a))
+    return a, task, ctl
+
+
+def test_checkpoint_schema_names_pruning_and_resume(tmp_path):
+    from hetseq_b200 import train as train_mod
+    a, task, ctl = _tiny_mnist_controller(tmp_path, max_epoch=2, keep_last_epochs=1)
+    train_mod.main(a)
+    files = sorted(os.listdir(a.save_dir))
+    assert files == ['checkpoint2.pt', 'checkpoint_last.pt']           # checkpoint1.pt pruned by --keep-last-epochs
+    st = checkpoint_utils.load_checkpoint_to_cpu(os.path.join(a.save_dir, 'checkpoint_last.pt'))
+    assert set(st) == {'args', 'model', 'optimizer_history', 'extra_state', 'last_optimizer_state'}
+    assert st['optimizer_history'][-1]['optimizer_name'] == '_Adadelta' and st['optimizer_history'][-1]['num_updates'] == 8
+    assert st['extra_state']['train_iterator'] == {'epoch': 2, 'iterations_in_epoch': 4}   # the reference writes {}
+    assert 'train_meters' in st['extra_state']
+    opt_state = st['last_optimizer_state']
+    assert set(opt_state['state'][0]) == {'step', 'square_avg', 'acc_delta'} and opt_state['state'][0]['square_avg'].dtype == torch.float32
+    # resume: a third epoch continues from update 8 with the restored optimizer state
+    a2, task2, ctl2 = _tiny_mnist_controller(tmp_path, max_epoch=3, keep_last_epochs=1)
+    extra, epoch_itr = checkpoint_utils.load_checkpoint(a2, ctl2)
+    assert ctl2.get_num_updates() == 8 and epoch_itr.epoch == 2 and ctl2.optimizer.step_count == 8
+    for k, v in ctl2.get_model().state_dict().items():
+        assert torch.equal(v, st['model'][k])
+    assert checkpoint_utils.checkpoint_paths(a.save_dir) == [os.path.join(a.save_dir, 'checkpoint2.pt')]
+
+
+def test_reference_style_checkpoint_without_extra_state_loads(tmp_path):
+    """A file as the reference writes it (extra_state == {}) loads model + optimizer instead of crashing
+    with KeyError('train_iterator') (reference controller.py:183)."""
+    a, task, ctl = _tiny_mnist_controller(tmp_path)
+    ctl.optimizer
+    os.makedirs(a.save_dir, exist_ok=True)
+    state = checkpoint_utils.build_state(a, ctl.get_model().state_dict(), '_Adadelta', ctl.optimizer.state_dict(),
+                                         ctl.lr_scheduler.state_dict(), 5, [], {})
+    checkpoint_utils.torch_persistent_save(state, os.path.join(a.save_dir, 'checkpoint_last.pt'))
+    a2, task2, ctl2 = _tiny_mnist_controller(tmp_path)
+    extra, itr = checkpoint_utils.load_checkpoint(a2, ctl2)
+    assert extra is None and ctl2.get_num_updates() == 5 and itr.epoch == 0
+
+
+def test_mid_epoch_checkpoint_and_exact_resume(tmp_path):
+    """--save-interval-updates works (unreachable in the reference) and a resumed run reproduces the
+    uninterrupted one bit for bit (iterator fast-forward + seed + optimizer state)."""
+    from hetseq_b200 import train as train_mod
+    full_dir = tmp_path / 'full'; full_dir.mkdir()
+    a, _, _ = _tiny_mnist_controller(full_dir, max_epoch=1)
+    ctl_full = train_mod.main(a)
+    part_dir = tmp_path / 'part'; part_dir.mkdir()
+    b, _, _ = _tiny_mnist_controller(part_dir, max_update=2, save_interval_updates=2, max_epoch=1, no_epoch_checkpoints=True)
+    train_mod.main(b)
+    assert 'checkpoint_1_2.pt' in os.listdir(b.save_dir)
+    c, _, _ = _tiny_mnist_controller(part_dir, max_epoch=1)
+    ctl_res = train_mod.main(c)
+    assert ctl_res.get_num_updates() == ctl_full.get_num_updates() == 4
+    for (k, v), (_, w) in zip(ctl_full.get_model().state_dict().items(), ctl_res.get_model().state_dict().items()):
+        assert torch.equal(v, w), k
+
+
+def test_all_gather_list_single_process():
+    from hetseq_b200.parallel import distributed_utils as du
+    assert du.all_gather_list({'a': 1}) == [{'a': 1}]
+    assert du.get_rank() == 0 and du.get_world_size() == 1
+
+
+def test_eval_mnist_cli(tmp_path, capsys):
+    from hetseq_b200 import eval_mnist, train as train_mod
+    a, _, _ = _tiny_mnist_controller(tmp_path, max_epoch=3)
+    train_mod.main(a)
+    loss, acc = eval_mnist.main(['--model_ckpt', os.path.join(a.save_dir, 'checkpoint_last.pt'), '--mnist_dir',
+                                 str(tmp_path / 'data'), '--device', 'cpu'])
+    assert 'Test set: Average loss' in capsys.readouterr().out and acc > 0.5
