@@ -22,6 +22,7 @@
 #include "host.h"
 #include "../include/hetseq_b200.h"
 
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 
@@ -53,9 +54,12 @@ struct GemmParams {
   int kb_per_split;
 };
 
-template <int BN> struct GemmCfg {
-  static constexpr int STAGES = (BN == 256) ? 4 : 6;
-  static constexpr int B_STAGE_BYTES = BN * 128;
+// CG = CTAs per MMA (tcgen05 cta_group). CG == 2: a CTA pair owns a 256 x BN tile; each CTA stages its own
+// 128 rows of A and its own BN/2 rows of B (the MMA reads B from both CTAs' smem), so a stage is 32 KiB
+// instead of 48 KiB and the ring is 6 deep -- more bytes in flight per SM for the same shared memory.
+template <int BN, int CG = 1> struct GemmCfg {
+  static constexpr int STAGES = (BN == 256 && CG == 1) ? 4 : 6;
+  static constexpr int B_STAGE_BYTES = (BN / CG) * 128;
   static constexpr int TMEM_COLS = 2 * BN;
   static constexpr int STAGING_BYTES = EPI_WARPS * 4096;  // one 32-row x 128-byte box per epilogue warp
   static constexpr int SMEM_BYTES = STAGES * (A_STAGE_BYTES + B_STAGE_BYTES) + STAGING_BYTES +
@@ -117,12 +121,15 @@ __device__ __forceinline__ void store_row32(T* __restrict__ p, int n0, int N, bo
 }
 
 // ---- the kernel -------------------------------------------------------------------------------
-template <int BN, typename InT, typename OutT>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
-gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                    const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmAux,
-                    const GemmParams p) {
-  using Cfg = GemmCfg<BN>;
+template <int BN, typename InT, typename OutT, int CG>
+__device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
+                                          const CUtensorMap& tmAux, const GemmParams& p) {
+  using Cfg = GemmCfg<BN, CG>;
+  constexpr int TILE_M = BM * CG;            // rows of C per work item
+  const int cta_rank = CG == 2 ? static_cast<int>(cluster_ctarank()) : 0;
+  const bool leader = cta_rank == 0;
+  const int worker = CG == 2 ? (blockIdx.x >> 1) : blockIdx.x;        // index of this CTA (pair) among the workers
+  const int nworkers = CG == 2 ? (gridDim.x >> 1) : gridDim.x;
   constexpr int STAGES = Cfg::STAGES;
   constexpr int B_STAGE_BYTES = Cfg::B_STAGE_BYTES;
 
@@ -155,15 +162,16 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       }
       for (int a = 0; a < 2; ++a) {
         mbar_init(&tfull_bar[a], 1);
-        mbar_init(&tempty_bar[a], EPI_WARPS);  // one arrive per epilogue warp
+        mbar_init(&tempty_bar[a], EPI_WARPS * CG);  // one arrive per epilogue warp (of both CTAs of a pair)
       }
       fence_mbar_init();
     }
     __syncwarp();
-    tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+    if constexpr (CG == 2) tmem_alloc_2cta(tmem_slot, Cfg::TMEM_COLS);
+    else tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
   }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (CG == 2) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -172,40 +180,46 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int work = blockIdx.x; work < num_work; work += gridDim.x) {
+      for (int work = worker; work < num_work; work += nworkers) {
         const int tile = work % num_tiles, ks = work / num_tiles;
         const int tm = tile % p.tiles_m, tn = tile / p.tiles_m;
         const int kb0 = ks * p.kb_per_split, kb1 = min(p.num_kb, kb0 + p.kb_per_split);
+        const int m_row = tm * TILE_M + cta_rank * BM;          // this CTA's rows of A
+        const int n_row = tn * BN + cta_rank * (BN / CG);       // this CTA's rows of B
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
-          mbar_expect_tx(&full_bar[stage], A_STAGE_BYTES + B_STAGE_BYTES);
+          // the leader's barrier collects the bytes of both CTAs of the pair
+          if (leader) mbar_expect_tx(&full_bar[stage], CG * (A_STAGE_BYTES + B_STAGE_BYTES));
           uint8_t* a_dst = sA + stage * A_STAGE_BYTES;
           uint8_t* b_dst = sB + stage * B_STAGE_BYTES;
+          auto load = [&](void* dst, const CUtensorMap* tm_, int c0, int c1) {
+            if constexpr (CG == 2) tma_load_2d_2cta(dst, tm_, &full_bar[stage], c0, c1);
+            else tma_load_2d(dst, tm_, &full_bar[stage], c0, c1);
+          };
           if (!p.a_mn) {
-            tma_load_2d(a_dst, &tmA, &full_bar[stage], kb * BK, tm * BM);
+            load(a_dst, &tmA, kb * BK, m_row);
           } else {
 #pragma unroll
-            for (int j = 0; j < BM / 64; ++j)
-              tma_load_2d(a_dst + j * (BK * 128), &tmA, &full_bar[stage], tm * BM + j * 64, kb * BK);
+            for (int j = 0; j < BM / 64; ++j) load(a_dst + j * (BK * 128), &tmA, m_row + j * 64, kb * BK);
           }
           if (!p.b_mn) {
-            tma_load_2d(b_dst, &tmB, &full_bar[stage], kb * BK, tn * BN);
+            load(b_dst, &tmB, kb * BK, n_row);
           } else {
 #pragma unroll
-            for (int j = 0; j < BN / 64; ++j)
-              tma_load_2d(b_dst + j * (BK * 128), &tmB, &full_bar[stage], tn * BN + j * 64, kb * BK);
+            for (int j = 0; j < BN / CG / 64; ++j) load(b_dst + j * (BK * 128), &tmB, n_row + j * 64, kb * BK);
           }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer =====================
+    // ===================== MMA issuer (leader CTA of a pair only) =====================
     int stage = 0;
     uint32_t phase = 0;
     int as = 0;
     uint32_t aphase = 0;
-    for (int work = blockIdx.x; work < num_work; work += gridDim.x) {
+    if (leader)
+    for (int work = worker; work < num_work; work += nworkers) {
       const int ks = work / num_tiles;
       const int kb0 = ks * p.kb_per_split, kb1 = min(p.num_kb, kb0 + p.kb_per_split);
       mbar_wait(&tempty_bar[as], aphase ^ 1);
@@ -221,11 +235,20 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           const uint64_t bdesc = umma_desc_sw128(b_addr, p.b_lbo, p.b_sbo);
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
-            umma_f16(d_tmem, adesc + ((k * p.a_kadv) >> 4), bdesc + ((k * p.b_kadv) >> 4), p.idesc,
-                     (kb != kb0 || k != 0) ? 1u : 0u);
+            if constexpr (CG == 2)
+              umma_f16_2cta(d_tmem, adesc + ((k * p.a_kadv) >> 4), bdesc + ((k * p.b_kadv) >> 4), p.idesc,
+                            (kb != kb0 || k != 0) ? 1u : 0u);
+            else
+              umma_f16(d_tmem, adesc + ((k * p.a_kadv) >> 4), bdesc + ((k * p.b_kadv) >> 4), p.idesc,
+                       (kb != kb0 || k != 0) ? 1u : 0u);
           }
-          umma_commit(&empty_bar[stage]);                  // ring slot free once these MMAs retire
-          if (kb == kb1 - 1) umma_commit(&tfull_bar[as]);   // accumulator complete
+          if constexpr (CG == 2) {
+            umma_commit_2cta(&empty_bar[stage], 3);                  // frees the slot in both CTAs
+            if (kb == kb1 - 1) umma_commit_2cta(&tfull_bar[as], 3);   // accumulator complete (both CTAs)
+          } else {
+            umma_commit(&empty_bar[stage]);                  // ring slot free once these MMAs retire
+            if (kb == kb1 - 1) umma_commit(&tfull_bar[as]);   // accumulator complete
+          }
         }
         __syncwarp();
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -245,14 +268,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     uint8_t* stg = sStage + (warp - 2) * 4096;
     int as = 0;
     uint32_t aphase = 0;
-    for (int work = blockIdx.x; work < num_work; work += gridDim.x) {
+    for (int work = worker; work < num_work; work += nworkers) {
       const int tile = work % num_tiles, ks = work / num_tiles;
       const int tm = tile % p.tiles_m, tn = tile / p.tiles_m;
       const int n_base = tn * BN;
       mbar_wait(&tfull_bar[as], aphase);
       __syncwarp();
       tc_fence_after();
-      const int m0 = tm * BM + q * 32;
+      const int m0 = tm * TILE_M + cta_rank * BM + q * 32;
       const int m = m0 + lane;
       const bool row_ok = m < p.M;
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
@@ -384,7 +407,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty_bar[as]);
+      if (lane == 0) {
+        if constexpr (CG == 2) mbar_arrive_leader(&tempty_bar[as]);   // the pair's MMA issuer lives in CTA 0
+        else mbar_arrive(&tempty_bar[as]);
+      }
       if (++as == 2) { as = 0; aphase ^= 1; }
     }
     // every bulk store of this warp must have completed before the CTA (and its smem) goes away
@@ -392,11 +418,30 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   }
 
   tc_fence_before();
-  __syncthreads();
+  if constexpr (CG == 2) cluster_sync_all();   // the leader's MMAs read the peer's smem: nobody leaves early
+  else __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+    if constexpr (CG == 2) tmem_dealloc_2cta(tmem_base, Cfg::TMEM_COLS);
+    else tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
   }
+}
+
+template <int BN, typename InT, typename OutT>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmAux,
+                    const GemmParams p) {
+  gemm_body<BN, InT, OutT, 1>(tmA, tmB, tmC, tmAux, p);
+}
+
+// CTA-pair variant: tcgen05.mma.cta_group::2 with UMMA_M = 256 (the pair's 256 x 256 tile)
+template <typename InT, typename OutT>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                         const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmAux,
+                         const GemmParams p) {
+  gemm_body<256, InT, OutT, 2>(tmA, tmB, tmC, tmAux, p);
 }
 
 // ---- host side --------------------------------------------------------------------------------
@@ -458,10 +503,13 @@ static int make_tmap_2d(CUtensorMap* out, const void* base, uint64_t inner, uint
   return 0;
 }
 
-template <int BN, typename InT, typename OutT>
+template <int BN, typename InT, typename OutT, int CG>
 static int launch_gemm(const hs_gemm_args& a, cudaStream_t stream) {
-  using Cfg = GemmCfg<BN>;
-  auto kern = gemm_tcgen05_kernel<BN, InT, OutT>;
+  using Cfg = GemmCfg<BN, CG>;
+  constexpr int TILE_M = BM * CG;
+  void (*kern)(CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, GemmParams);
+  if constexpr (CG == 2) kern = gemm_tcgen05_2cta_kernel<InT, OutT>;
+  else kern = gemm_tcgen05_kernel<BN, InT, OutT>;
   static bool attr_done[64] = {false};
   int dev = 0;
   HS_CUDA_OK(cudaGetDevice(&dev));
@@ -474,18 +522,18 @@ static int launch_gemm(const hs_gemm_args& a, cudaStream_t stream) {
   if (!a.a_mn_major) rc = make_tmap_2d_16b(&tmA, a.A, a.K, a.M, a.lda, BK, BM);
   else               rc = make_tmap_2d_16b(&tmA, a.A, a.M, a.K, a.lda, 64, BK);
   if (rc) return rc;
-  if (!a.b_mn_major) rc = make_tmap_2d_16b(&tmB, a.B, a.K, a.N, a.ldb, BK, BN);
+  if (!a.b_mn_major) rc = make_tmap_2d_16b(&tmB, a.B, a.K, a.N, a.ldb, BK, BN / CG);
   else               rc = make_tmap_2d_16b(&tmB, a.B, a.N, a.K, a.ldb, 64, BK);
   if (rc) return rc;
 
   GemmParams p;
   p.C = a.C; p.bias = a.bias; p.aux_out = a.aux_out; p.aux_in = a.aux_in;
   p.M = a.M; p.N = a.N; p.K = a.K; p.ldc = a.ldc; p.ldaux = a.ldaux;
-  p.tiles_m = (a.M + BM - 1) / BM;
+  p.tiles_m = (a.M + TILE_M - 1) / TILE_M;
   p.tiles_n = (a.N + BN - 1) / BN;
   p.num_kb = (a.K + BK - 1) / BK;
   p.a_mn = a.a_mn_major; p.b_mn = a.b_mn_major;
-  p.idesc = umma_idesc_f16(a.in_dtype == HS_BF16 ? 1 : 0, a.a_mn_major, a.b_mn_major, BM, BN);
+  p.idesc = umma_idesc_f16(a.in_dtype == HS_BF16 ? 1 : 0, a.a_mn_major, a.b_mn_major, TILE_M, BN);
   // K-major, 128B swizzle: 8-row groups 1024 B apart; a k-step of 16 elements is 32 B inside the row.
   // MN-major, 128B swizzle: 64-element MN groups are separate TMA boxes (BK*128 B apart), 8-k groups
   // 1024 B apart; a k-step of 16 rows is 2048 B.
@@ -501,7 +549,7 @@ static int launch_gemm(const hs_gemm_args& a, cudaStream_t stream) {
   p.tma_store = (vec && !(a.accumulate && sizeof(OutT) == 2)) ? 1 : 0;
 
   const int tiles = p.tiles_m * p.tiles_n;
-  const int sms = num_sms();
+  const int sms = num_sms() / CG;   // workers: SMs, or SM pairs
   // split-K: only with the reduce-add epilogue (C already holds a valid partial sum) and no per-column work
   p.split_k = 1;
   if (p.tma_store && a.accumulate && a.bias == nullptr && a.act == HS_ACT_NONE && tiles < sms) {
@@ -524,19 +572,19 @@ static int launch_gemm(const hs_gemm_args& a, cudaStream_t stream) {
     if (a.aux_out != nullptr && make_tmap_2d(&tmAux, a.aux_out, a.N, a.M, a.ldaux, 64, 32, 2)) return 1;
   }
   const int work = tiles * p.split_k;
-  const int grid = work < sms ? work : sms;
+  const int grid = (work < sms ? work : sms) * CG;
   kern<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, tmC, tmAux, p);
   return post_launch("gemm_tcgen05_kernel");
 }
 
-template <int BN>
+template <int BN, int CG>
 static int dispatch_types(const hs_gemm_args& a, cudaStream_t s) {
   if (a.in_dtype == HS_F16) {
-    if (a.out_dtype == HS_F16) return launch_gemm<BN, __half, __half>(a, s);
-    if (a.out_dtype == HS_F32) return launch_gemm<BN, __half, float>(a, s);
+    if (a.out_dtype == HS_F16) return launch_gemm<BN, __half, __half, CG>(a, s);
+    if (a.out_dtype == HS_F32) return launch_gemm<BN, __half, float, CG>(a, s);
   } else if (a.in_dtype == HS_BF16) {
-    if (a.out_dtype == HS_BF16) return launch_gemm<BN, __nv_bfloat16, __nv_bfloat16>(a, s);
-    if (a.out_dtype == HS_F32) return launch_gemm<BN, __nv_bfloat16, float>(a, s);
+    if (a.out_dtype == HS_BF16) return launch_gemm<BN, __nv_bfloat16, __nv_bfloat16, CG>(a, s);
+    if (a.out_dtype == HS_F32) return launch_gemm<BN, __nv_bfloat16, float, CG>(a, s);
   }
   set_last_error("hs_gemm: unsupported dtype combination in=%d out=%d", a.in_dtype, a.out_dtype);
   return 1;
@@ -565,5 +613,10 @@ extern "C" int hs_gemm(const hs_gemm_args* args, hs_stream_t stream) {
   };
   const bool use256 = a.N > 128 && waves_cost(t256, 256) <= waves_cost(t128, 128);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  return use256 ? dispatch_types<256>(a, s) : dispatch_types<128>(a, s);
+  // CTA pairs (cta_group::2, 256 x 256 tiles) whenever the problem has at least one full pair tile;
+  // HETSEQ_GEMM_CTA_GROUP=1 forces the single-CTA kernel (debugging / comparison)
+  static const int force_cg = [] { const char* e = getenv("HETSEQ_GEMM_CTA_GROUP"); return e ? atoi(e) : 0; }();
+  const bool pair = force_cg == 2 || (force_cg != 1 && a.M >= 256 && a.N > 128);
+  if (pair) return dispatch_types<256, 2>(a, s);
+  return use256 ? dispatch_types<256, 1>(a, s) : dispatch_types<128, 1>(a, s);
 }
