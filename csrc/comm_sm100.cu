@@ -30,6 +30,10 @@
 namespace hs {
 
 constexpr int DP_THREADS = 512;
+// The reduce-scatter runs WHILE backward's GEMMs own the SMs (320 threads x 168 registers, ~225 KB smem per
+// SM). It only overlaps if its CTAs fit into what is left of an SM: no shared memory to speak of and
+// <= 11.7 K registers. 256 threads at <= 42 registers (launch bound 6 CTAs/SM) is 10.5 K.
+constexpr int RS_THREADS = 256;
 constexpr int DP_MAX_WORLD = 16;
 
 // signal pad layout (32-bit words)
@@ -77,11 +81,11 @@ __device__ __forceinline__ void wait_flag(const uint32_t* p, uint32_t want, cons
 }
 
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(DP_THREADS)
+__global__ void __launch_bounds__(RS_THREADS, 6)
 dp_reduce_scatter_kernel(PeerTable grads, PeerTable sigs, int rank, int W, long long chunk_begin,
                          long long chunk_end, int chunk, int slot, uint32_t epoch, const uint32_t* __restrict__ epoch_dev,
                          float* __restrict__ sumsq_accum) {
-  __shared__ float red[32];
+  __shared__ float red[RS_THREADS / 32];
   if (epoch_dev != nullptr) epoch = *epoch_dev;
   // 1. announce + wait (block 0 announces; every block waits on its own before touching peer data)
   if (blockIdx.x == 0 && threadIdx.x < W) {
@@ -102,16 +106,28 @@ dp_reduce_scatter_kernel(PeerTable grads, PeerTable sigs, int rank, int W, long 
   float* mine = reinterpret_cast<float*>(grads.ptr[rank]);
   for (long long c = first + static_cast<long long>(blockIdx.x) * W; c < chunk_end; c += static_cast<long long>(gridDim.x) * W) {
     const long long base = c * chunk;
-    for (int i = threadIdx.x; i < vec_per_chunk; i += blockDim.x) {
-      float4 s = reinterpret_cast<const float4*>(mine + base)[i];
-#pragma unroll 4
+    // two vectors per thread and all peers' loads issued before the first add: (W-1)*2 NVLink loads in flight
+    for (int i = threadIdx.x; i < vec_per_chunk; i += 2 * blockDim.x) {
+      const int i2 = i + blockDim.x;
+      const bool has2 = i2 < vec_per_chunk;
+      float4 s0 = reinterpret_cast<const float4*>(mine + base)[i];
+      float4 s1 = has2 ? reinterpret_cast<const float4*>(mine + base)[i2] : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 2
       for (int p = 1; p < W; ++p) {
         const int peer = (rank + p) % W;   // stagger peers so that ranks do not all hit the same GPU at once
-        const float4 v = ld_relaxed_sys_f4(reinterpret_cast<const float4*>(reinterpret_cast<const float*>(grads.ptr[peer]) + base) + i);
-        s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+        const float4* src = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(grads.ptr[peer]) + base);
+        const float4 v0 = ld_relaxed_sys_f4(src + i);
+        float4 v1 = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (has2) v1 = ld_relaxed_sys_f4(src + i2);
+        s0.x += v0.x; s0.y += v0.y; s0.z += v0.z; s0.w += v0.w;
+        s1.x += v1.x; s1.y += v1.y; s1.z += v1.z; s1.w += v1.w;
       }
-      reinterpret_cast<float4*>(mine + base)[i] = s;
-      acc += s.x * s.x + s.y * s.y + s.z * s.z + s.w * s.w;
+      reinterpret_cast<float4*>(mine + base)[i] = s0;
+      acc += s0.x * s0.x + s0.y * s0.y + s0.z * s0.z + s0.w * s0.w;
+      if (has2) {
+        reinterpret_cast<float4*>(mine + base)[i2] = s1;
+        acc += s1.x * s1.x + s1.y * s1.y + s1.z * s1.z + s1.w * s1.w;
+      }
     }
   }
   // 3. norm partial
@@ -286,9 +302,9 @@ extern "C" int hs_dp_reduce_scatter(void* const* grad_ptrs, void* const* sig_ptr
     return 1;
   }
   const long long owned = (chunk_end - chunk_begin + W - 1) / W;
-  int grid = nblocks > 0 ? nblocks : 64;
+  int grid = nblocks > 0 ? nblocks : num_sms();
   if (grid > owned) grid = static_cast<int>(owned < 1 ? 1 : owned);
-  dp_reduce_scatter_kernel<<<grid, DP_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(g, s, rank, W, chunk_begin, chunk_end, chunk, slot, epoch, epoch_dev, sumsq_accum);
+  dp_reduce_scatter_kernel<<<grid, RS_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(g, s, rank, W, chunk_begin, chunk_end, chunk, slot, epoch, epoch_dev, sumsq_accum);
   return post_launch("dp_reduce_scatter_kernel");
 }
 

@@ -114,7 +114,8 @@ class FusedBackend(AllReduceBackend):
         # the update number lives in device memory and is bumped by a tiny device op per update, so the
         # very same kernel arguments stay valid when the step is replayed from a CUDA graph
         self.epoch_t = torch.zeros(1, dtype=torch.int32, device=dev)
-        self.rs_blocks = int(getattr(args, 'fused_rs_blocks', 0) or 48)
+        import os
+        self.rs_blocks = int(os.environ.get('HETSEQ_RS_BLOCKS', '0') or getattr(args, 'fused_rs_blocks', 0) or 296)
         torch.cuda.synchronize()
         dist.barrier(group=self.group, device_ids=[dev.index])
 
