@@ -26,7 +26,7 @@ namespace hs {
 
 constexpr int AT_S = 128;   // queries and keys per tile
 constexpr int AT_D = 64;    // head dim
-constexpr int AT_THREADS = 128;
+constexpr int AT_THREADS = 256;   // two threads per query row (column halves)
 constexpr int TILE_BYTES = AT_S * 128;       // [128 rows x 64 x 16-bit], 128B rows, SW128
 constexpr int PBUF_BYTES = 2 * TILE_BYTES;   // [128 x 128] 16-bit as two 64-column SW128 regions
 
@@ -36,6 +36,7 @@ struct AttnParams {
   const void* o;          // bwd: forward output [M, H]
   const void* dout;       // bwd: dO [M, H] (also via tensor map)
   float* lse;             // [B*heads*S]
+  float* dbias;           // bwd, optional: fp32 [3H] += column sums of dqkv (the q/k/v bias gradient)
   int B, heads, H;
   float scale, p;
   const long long* seed;
@@ -44,15 +45,6 @@ struct AttnParams {
 
 __device__ __forceinline__ uint32_t sw128_offset(int row, int col16 /*16-byte chunk 0..7*/) {
   return static_cast<uint32_t>(row * 128 + ((col16 ^ (row & 7)) << 4));
-}
-
-// keep-scale for 4 consecutive key columns of one query row
-__device__ __forceinline__ void drop4(const long long* seed_ptr, uint32_t site, uint64_t e0, float p, float inv,
-                                      float (&mk)[4]) {
-  const uint64_t seed = static_cast<uint64_t>(seed_ptr[0]) * 0x9E3779B97F4A7C15ull + static_cast<uint64_t>(seed_ptr[1]);
-  const float4 r = philox_uniform4(seed, site, e0 >> 2);
-  mk[0] = r.x >= p ? inv : 0.f; mk[1] = r.y >= p ? inv : 0.f;
-  mk[2] = r.z >= p ? inv : 0.f; mk[3] = r.w >= p ? inv : 0.f;
 }
 
 template <typename T>
@@ -66,6 +58,8 @@ __device__ __forceinline__ void store_row_chunk8(uint8_t* buf, int row, int col0
 }
 
 // ------------------------------------------------------------------------------------------------
+// 256 threads: warp w reads TMEM lane quarter (w & 3) -- query rows 32*(w&3) .. +31 -- and the column half
+// (w >> 2); the two threads of a row meet through 1 KB of shared memory for the row max and the row sum.
 template <typename T>
 __global__ void __launch_bounds__(AT_THREADS, 2)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams P) {
@@ -76,10 +70,13 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams P) {
   uint8_t* sV = sK + TILE_BYTES;
   uint8_t* sP = sV + TILE_BYTES;
   float* sMask = reinterpret_cast<float*>(sP + PBUF_BYTES);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sMask + AT_S);
+  float* sRed = sMask + AT_S;                       // [2][128] row max / row sum halves
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sRed + 2 * AT_S);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int q = warp & 3, hf = warp >> 2;
+  const int r = q * 32 + lane;                      // query row of this thread
   const int b = blockIdx.x / P.heads, h = blockIdx.x % P.heads;
   const int row0 = b * AT_S;
 
@@ -94,7 +91,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams P) {
     __syncwarp();
     tmem_alloc(tmem_slot, 256);
   }
-  sMask[tid] = P.mask[b * AT_S + tid];
+  if (tid < AT_S) sMask[tid] = P.mask[b * AT_S + tid] * 1.4426950408889634f;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -119,45 +116,54 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams P) {
   __syncwarp();
   tc_fence_after();
 
-  // ---- softmax: thread `tid` owns query row `tid` ----
-  const uint32_t t_row = tmem + (static_cast<uint32_t>(warp * 32) << 16);
+  // ---- softmax: this thread owns 64 key columns of query row r ----
+  constexpr int HC = AT_S / 2;
+  const int col0 = hf * HC;
+  const uint32_t t_row = tmem + (static_cast<uint32_t>(q * 32) << 16);
   const float sl2 = P.scale * 1.4426950408889634f;   // fold log2(e) into the scale
-  float s[AT_S];
+  float s[HC];
 #pragma unroll
-  for (int c = 0; c < AT_S / 32; ++c) {
-    uint32_t r[32];
-    tmem_ld_32x32(t_row + c * 32, r);
+  for (int c = 0; c < HC / 32; ++c) {
+    uint32_t rr[32];
+    tmem_ld_32x32(t_row + col0 + c * 32, rr);
     tmem_ld_wait();
 #pragma unroll
-    for (int i = 0; i < 32; ++i) s[c * 32 + i] = __uint_as_float(r[i]) * sl2 + sMask[c * 32 + i] * 1.4426950408889634f;
+    for (int i = 0; i < 32; ++i) s[c * 32 + i] = __uint_as_float(rr[i]) * sl2 + sMask[col0 + c * 32 + i];
   }
   float mx = -INFINITY;
 #pragma unroll
-  for (int i = 0; i < AT_S; ++i) mx = fmaxf(mx, s[i]);
+  for (int i = 0; i < HC; ++i) mx = fmaxf(mx, s[i]);
+  sRed[hf * AT_S + r] = mx;
+  __syncthreads();
+  mx = fmaxf(mx, sRed[(hf ^ 1) * AT_S + r]);
+  __syncthreads();
   float l = 0.f;
 #pragma unroll
-  for (int i = 0; i < AT_S; ++i) { s[i] = exp2f(s[i] - mx); l += s[i]; }
+  for (int i = 0; i < HC; ++i) { s[i] = exp2f(s[i] - mx); l += s[i]; }
+  sRed[hf * AT_S + r] = l;
   const bool drop = P.p > 0.f;
   const float inv_keep = drop ? 1.f / (1.f - P.p) : 1.f;
-  const uint64_t e_row = (static_cast<uint64_t>(blockIdx.x) * AT_S + tid) * AT_S;
+  const uint64_t seed = drop ? philox_seed(P.seed) : 0ull;
+  const uint32_t thr = dropout_thr16(P.p);
+  const uint64_t e_row = (static_cast<uint64_t>(blockIdx.x) * AT_S + r) * AT_S;
 #pragma unroll
-  for (int c8 = 0; c8 < AT_S / 8; ++c8) {
+  for (int c8 = 0; c8 < HC / 8; ++c8) {
     float v[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) v[i] = s[c8 * 8 + i];
     if (drop) {
-      float m0[4], m1[4];
-      drop4(P.seed, P.site, e_row + c8 * 8, P.p, inv_keep, m0);
-      drop4(P.seed, P.site, e_row + c8 * 8 + 4, P.p, inv_keep, m1);
+      float mk[8];
+      philox_keep8(seed, P.site, (e_row + col0 + c8 * 8) >> 3, thr, inv_keep, mk);
 #pragma unroll
-      for (int i = 0; i < 4; ++i) { v[i] *= m0[i]; v[4 + i] *= m1[i]; }
+      for (int i = 0; i < 8; ++i) v[i] *= mk[i];
     }
-    store_row_chunk8<T>(sP, tid, c8 * 8, v);
+    store_row_chunk8<T>(sP, r, col0 + c8 * 8, v);
   }
-  if (P.lse) P.lse[static_cast<size_t>(blockIdx.x) * AT_S + tid] = (mx + log2f(l)) * 0.6931471805599453f;
   fence_proxy_async_smem();
   tc_fence_before();
   __syncthreads();
+  l += sRed[(hf ^ 1) * AT_S + r];
+  if (P.lse && hf == 0) P.lse[static_cast<size_t>(blockIdx.x) * AT_S + r] = (mx + log2f(l)) * 0.6931471805599453f;
 
   if (tid == 0) {
     tc_fence_after();
@@ -177,21 +183,18 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams P) {
   tc_fence_after();
   {
     const float inv_l = 1.f / l;
-    T* dst = reinterpret_cast<T*>(P.out) + static_cast<size_t>(row0 + tid) * P.H + h * AT_D;
+    T* dst = reinterpret_cast<T*>(P.out) + static_cast<size_t>(row0 + r) * P.H + h * AT_D + hf * 32;
+    uint32_t rr[32];
+    tmem_ld_32x32(t_row + 128 + hf * 32, rr);
+    tmem_ld_wait();
 #pragma unroll
-    for (int c = 0; c < 2; ++c) {
-      uint32_t r[32];
-      tmem_ld_32x32(t_row + 128 + c * 32, r);
-      tmem_ld_wait();
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        uint4 u;
-        u.x = Cvt<T>::pack2(__uint_as_float(r[i * 8 + 0]) * inv_l, __uint_as_float(r[i * 8 + 1]) * inv_l);
-        u.y = Cvt<T>::pack2(__uint_as_float(r[i * 8 + 2]) * inv_l, __uint_as_float(r[i * 8 + 3]) * inv_l);
-        u.z = Cvt<T>::pack2(__uint_as_float(r[i * 8 + 4]) * inv_l, __uint_as_float(r[i * 8 + 5]) * inv_l);
-        u.w = Cvt<T>::pack2(__uint_as_float(r[i * 8 + 6]) * inv_l, __uint_as_float(r[i * 8 + 7]) * inv_l);
-        reinterpret_cast<uint4*>(dst + c * 32)[i] = u;
-      }
+    for (int i = 0; i < 4; ++i) {
+      uint4 u;
+      u.x = Cvt<T>::pack2(__uint_as_float(rr[i * 8 + 0]) * inv_l, __uint_as_float(rr[i * 8 + 1]) * inv_l);
+      u.y = Cvt<T>::pack2(__uint_as_float(rr[i * 8 + 2]) * inv_l, __uint_as_float(rr[i * 8 + 3]) * inv_l);
+      u.z = Cvt<T>::pack2(__uint_as_float(rr[i * 8 + 4]) * inv_l, __uint_as_float(rr[i * 8 + 5]) * inv_l);
+      u.w = Cvt<T>::pack2(__uint_as_float(rr[i * 8 + 6]) * inv_l, __uint_as_float(rr[i * 8 + 7]) * inv_l);
+      reinterpret_cast<uint4*>(dst)[i] = u;
     }
   }
   tc_fence_before();
@@ -203,8 +206,16 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams P) {
 }
 
 // ------------------------------------------------------------------------------------------------
+// Backward, 256 threads, two CTAs per SM (96 KB of shared memory and 256 TMEM columns each):
+//   phase 0  TMA Q,K,V,dO -> S = Q K^T (TMEM 0..127), dP = dO V^T (128..255)
+//   phase 1  thread (row, column half): P = exp2(s - lse) with the dropout mask recomputed -> shared memory;
+//            dS = P (dP - D) / sqrt(d) stays in registers as 32 packed 16-bit pairs
+//   phase 2  dV = P^T dO into TMEM 0..63 (S is dead); when it has retired the same 32 KB buffer is
+//            overwritten with dS and dK = dS^T Q (64..127), dQ = dS K (128..191) follow
+//   phase 3  dQ,dK,dV to the packed [M,3H] gradient; their column sums -- the q/k/v bias gradient -- are
+//            folded over the warp by a butterfly, over the CTA in shared memory, then 192 REDs per CTA.
 template <typename T>
-__global__ void __launch_bounds__(AT_THREADS, 1)
+__global__ void __launch_bounds__(AT_THREADS, 2)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
                 const AttnParams P) {
   extern __shared__ uint8_t smem_raw[];
@@ -213,13 +224,15 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
   uint8_t* sK = sQ + TILE_BYTES;
   uint8_t* sV = sK + TILE_BYTES;
   uint8_t* sDO = sV + TILE_BYTES;
-  uint8_t* sP = sDO + TILE_BYTES;
-  uint8_t* sDS = sP + PBUF_BYTES;
-  float* sMask = reinterpret_cast<float*>(sDS + PBUF_BYTES);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sMask + AT_S);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3);
+  uint8_t* sPD = sDO + TILE_BYTES;            // P, later dS
+  float* sMask = reinterpret_cast<float*>(sPD + PBUF_BYTES);
+  float* sBias = sMask + AT_S;                // [3][64] column sums of dQ, dK, dV
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sBias + 3 * AT_D);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
 
-  const int tid = threadIdx.x, warp = tid >> 5;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int q = warp & 3, hf = warp >> 2;
+  const int r = q * 32 + lane;
   const int b = blockIdx.x / P.heads, h = blockIdx.x % P.heads;
   const int row0 = b * AT_S;
   const int fmt = std::is_same<T, __nv_bfloat16>::value ? 1 : 0;
@@ -230,18 +243,19 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     mbar_init(&bars[0], 1);
     mbar_init(&bars[1], 1);
     mbar_init(&bars[2], 1);
+    mbar_init(&bars[3], 1);
     fence_mbar_init();
   }
   if (warp == 0) {
     __syncwarp();
-    tmem_alloc(tmem_slot, 512);
+    tmem_alloc(tmem_slot, 256);
   }
-  sMask[tid] = P.mask[b * AT_S + tid];
+  if (tid < AT_S) sMask[tid] = P.mask[b * AT_S + tid] * 1.4426950408889634f;
+  if (tid < 3 * AT_D) sBias[tid] = 0.f;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
-  // TMEM columns: S [0,128)  dP [128,256)  dV [256,320)  dK [320,384)  dQ [384,448)
 
   if (tid == 0) {
     mbar_expect_tx(&bars[0], 4 * TILE_BYTES);
@@ -266,8 +280,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
   // while the MMAs run: D = rowsum(dO * O) for this thread's query row, straight from global memory
   float Dq = 0.f;
   {
-    const T* o = reinterpret_cast<const T*>(P.o) + static_cast<size_t>(row0 + tid) * P.H + h * AT_D;
-    const T* d = reinterpret_cast<const T*>(P.dout) + static_cast<size_t>(row0 + tid) * P.H + h * AT_D;
+    const T* o = reinterpret_cast<const T*>(P.o) + static_cast<size_t>(row0 + r) * P.H + h * AT_D;
+    const T* d = reinterpret_cast<const T*>(P.dout) + static_cast<size_t>(row0 + r) * P.H + h * AT_D;
 #pragma unroll
     for (int i = 0; i < AT_D / 8; ++i) {
       const uint4 uo = reinterpret_cast<const uint4*>(o)[i], ud = reinterpret_cast<const uint4*>(d)[i];
@@ -276,108 +290,139 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
       Dq += o0.x * d0.x + o0.y * d0.y + o1.x * d1.x + o1.y * d1.y + o2.x * d2.x + o2.y * d2.y + o3.x * d3.x + o3.y * d3.y;
     }
   }
-  const float lse2 = P.lse[static_cast<size_t>(blockIdx.x) * AT_S + tid] * 1.4426950408889634f;
+  const float lse2 = P.lse[static_cast<size_t>(blockIdx.x) * AT_S + r] * 1.4426950408889634f;
   mbar_wait(&bars[1], 0);
   __syncwarp();
   tc_fence_after();
 
-  const uint32_t t_row = tmem + (static_cast<uint32_t>(warp * 32) << 16);
+  constexpr int HC = AT_S / 2;
+  const int col0 = hf * HC;
+  const uint32_t t_row = tmem + (static_cast<uint32_t>(q * 32) << 16);
   const float sl2 = P.scale * 1.4426950408889634f;
   const bool drop = P.p > 0.f;
   const float inv_keep = drop ? 1.f / (1.f - P.p) : 1.f;
-  const uint64_t e_row = (static_cast<uint64_t>(blockIdx.x) * AT_S + tid) * AT_S;
-#pragma unroll 1
-  for (int c = 0; c < AT_S / 32; ++c) {
+  const uint64_t seed = drop ? philox_seed(P.seed) : 0ull;
+  const uint32_t thr = dropout_thr16(P.p);
+  const uint64_t e_row = (static_cast<uint64_t>(blockIdx.x) * AT_S + r) * AT_S;
+  uint32_t dsp[HC / 2];                        // dS of this thread's 64 columns, packed 16-bit pairs
+#pragma unroll
+  for (int c = 0; c < HC / 32; ++c) {
     uint32_t rs[32], rd[32];
-    tmem_ld_32x32(t_row + c * 32, rs);
-    tmem_ld_32x32(t_row + 128 + c * 32, rd);
+    tmem_ld_32x32(t_row + col0 + c * 32, rs);
+    tmem_ld_32x32(t_row + 128 + col0 + c * 32, rd);
     tmem_ld_wait();
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
-      float pv[8], dsv[8], mk[8];
+      float pv[8], mk[8];
       if (drop) {
-        float m0[4], m1[4];
-        drop4(P.seed, P.site, e_row + c * 32 + g * 8, P.p, inv_keep, m0);
-        drop4(P.seed, P.site, e_row + c * 32 + g * 8 + 4, P.p, inv_keep, m1);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) { mk[i] = m0[i]; mk[4 + i] = m1[i]; }
+        philox_keep8(seed, P.site, (e_row + col0 + c * 32 + g * 8) >> 3, thr, inv_keep, mk);
       } else {
 #pragma unroll
         for (int i = 0; i < 8; ++i) mk[i] = 1.f;
       }
+      float dsv[8];
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
-        const int col = c * 32 + g * 8 + i;
-        const float p = exp2f(__uint_as_float(rs[g * 8 + i]) * sl2 + sMask[col] * 1.4426950408889634f - lse2);
+        const int col = col0 + c * 32 + g * 8 + i;
+        const float p = exp2f(__uint_as_float(rs[g * 8 + i]) * sl2 + sMask[col] - lse2);
         const float dp = __uint_as_float(rd[g * 8 + i]) * mk[i];
         pv[i] = p * mk[i];                        // dropped probabilities (what multiplied V in forward)
         dsv[i] = p * (dp - Dq) * P.scale;         // d(scores) including the 1/sqrt(d)
       }
-      store_row_chunk8<T>(sP, tid, c * 32 + g * 8, pv);
-      store_row_chunk8<T>(sDS, tid, c * 32 + g * 8, dsv);
+      store_row_chunk8<T>(sPD, r, col0 + c * 32 + g * 8, pv);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) dsp[c * 16 + g * 4 + i] = Cvt<T>::pack2(dsv[2 * i], dsv[2 * i + 1]);
     }
   }
   fence_proxy_async_smem();
   tc_fence_before();
   __syncthreads();
 
+  const uint32_t id_mm = umma_idesc_f16(fmt, 1, 1, 128, 64);   // A MN-major, B MN-major
+  const uint32_t id_km = umma_idesc_f16(fmt, 0, 1, 128, 64);   // A K-major,  B MN-major
   if (tid == 0) {
     tc_fence_after();
-    const uint32_t id_mm = umma_idesc_f16(fmt, 1, 1, 128, 64);   // A MN-major, B MN-major
-    const uint32_t id_km = umma_idesc_f16(fmt, 0, 1, 128, 64);   // A K-major,  B MN-major
 #pragma unroll
     for (int kk = 0; kk < AT_S / 16; ++kk) {
       // reduction over queries: 16 query rows per step = 2048 B in every operand
-      const uint64_t aP = umma_desc_sw128(smem_u32(sP) + kk * 2048, TILE_BYTES, 1024);
-      const uint64_t aDS = umma_desc_sw128(smem_u32(sDS) + kk * 2048, TILE_BYTES, 1024);
+      const uint64_t aP = umma_desc_sw128(smem_u32(sPD) + kk * 2048, TILE_BYTES, 1024);
       const uint64_t bDO = umma_desc_sw128(smem_u32(sDO) + kk * 2048, TILE_BYTES, 1024);
-      const uint64_t bQ = umma_desc_sw128(smem_u32(sQ) + kk * 2048, TILE_BYTES, 1024);
-      umma_f16(tmem + 256, aP, bDO, id_mm, kk != 0);    // dV[k,d] += P_drop^T dO
-      umma_f16(tmem + 320, aDS, bQ, id_mm, kk != 0);    // dK[k,d] += dS^T Q
-      // reduction over keys: dS K-major (two 64-wide regions), K tile MN-major
-      const uint64_t aDSk = umma_desc_sw128(smem_u32(sDS) + (kk >> 2) * TILE_BYTES + (kk & 3) * 32, 16, 1024);
-      const uint64_t bK = umma_desc_sw128(smem_u32(sK) + kk * 2048, TILE_BYTES, 1024);
-      umma_f16(tmem + 384, aDSk, bK, id_km, kk != 0);   // dQ[q,d] += dS K
+      umma_f16(tmem, aP, bDO, id_mm, kk != 0);          // dV[k,d] += P_drop^T dO
     }
     umma_commit(&bars[2]);
   }
-  mbar_wait(&bars[2], 0);
+  mbar_wait(&bars[2], 0);       // P has been consumed: the buffer can take dS
+  __syncwarp();
+  tc_fence_after();
+#pragma unroll
+  for (int c8 = 0; c8 < HC / 8; ++c8) {
+    const int col = col0 + c8 * 8;
+    const int region = col >> 6, c16 = (col & 63) >> 3;
+    *reinterpret_cast<uint4*>(sPD + region * TILE_BYTES + sw128_offset(r, c16)) =
+        make_uint4(dsp[c8 * 4 + 0], dsp[c8 * 4 + 1], dsp[c8 * 4 + 2], dsp[c8 * 4 + 3]);
+  }
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  if (tid == 0) {
+    tc_fence_after();
+#pragma unroll
+    for (int kk = 0; kk < AT_S / 16; ++kk) {
+      const uint64_t aDS = umma_desc_sw128(smem_u32(sPD) + kk * 2048, TILE_BYTES, 1024);
+      const uint64_t bQ = umma_desc_sw128(smem_u32(sQ) + kk * 2048, TILE_BYTES, 1024);
+      umma_f16(tmem + 64, aDS, bQ, id_mm, kk != 0);     // dK[k,d] += dS^T Q
+      // reduction over keys: dS K-major (two 64-wide regions), K tile MN-major
+      const uint64_t aDSk = umma_desc_sw128(smem_u32(sPD) + (kk >> 2) * TILE_BYTES + (kk & 3) * 32, 16, 1024);
+      const uint64_t bK = umma_desc_sw128(smem_u32(sK) + kk * 2048, TILE_BYTES, 1024);
+      umma_f16(tmem + 128, aDSk, bK, id_km, kk != 0);   // dQ[q,d] += dS K
+    }
+    umma_commit(&bars[3]);
+  }
+  mbar_wait(&bars[3], 0);
   __syncwarp();
   tc_fence_after();
   {
-    T* base = reinterpret_cast<T*>(P.out) + static_cast<size_t>(row0 + tid) * (3 * P.H) + h * AT_D;
+    T* base = reinterpret_cast<T*>(P.out) + static_cast<size_t>(row0 + r) * (3 * P.H) + h * AT_D + hf * 32;
 #pragma unroll
     for (int which = 0; which < 3; ++which) {
-      // which: 0 -> dQ (TMEM 384), 1 -> dK (320), 2 -> dV (256)
-      const uint32_t col = which == 0 ? 384u : (which == 1 ? 320u : 256u);
+      // which: 0 -> dQ (TMEM 128), 1 -> dK (64), 2 -> dV (0); this thread: 32 of the 64 columns
+      const uint32_t col = which == 0 ? 128u : (which == 1 ? 64u : 0u);
       T* dst = base + which * P.H;
+      uint32_t rr[32];
+      tmem_ld_32x32(t_row + col + hf * 32, rr);
+      tmem_ld_wait();
 #pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32(t_row + col + c * 32, r);
-        tmem_ld_wait();
+      for (int i = 0; i < 4; ++i) {
+        uint4 u;
+        u.x = Cvt<T>::pack2(__uint_as_float(rr[i * 8 + 0]), __uint_as_float(rr[i * 8 + 1]));
+        u.y = Cvt<T>::pack2(__uint_as_float(rr[i * 8 + 2]), __uint_as_float(rr[i * 8 + 3]));
+        u.z = Cvt<T>::pack2(__uint_as_float(rr[i * 8 + 4]), __uint_as_float(rr[i * 8 + 5]));
+        u.w = Cvt<T>::pack2(__uint_as_float(rr[i * 8 + 6]), __uint_as_float(rr[i * 8 + 7]));
+        reinterpret_cast<uint4*>(dst)[i] = u;
+      }
+      if (P.dbias != nullptr) {
+        float cs[32];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          uint4 u;
-          u.x = Cvt<T>::pack2(__uint_as_float(r[i * 8 + 0]), __uint_as_float(r[i * 8 + 1]));
-          u.y = Cvt<T>::pack2(__uint_as_float(r[i * 8 + 2]), __uint_as_float(r[i * 8 + 3]));
-          u.z = Cvt<T>::pack2(__uint_as_float(r[i * 8 + 4]), __uint_as_float(r[i * 8 + 5]));
-          u.w = Cvt<T>::pack2(__uint_as_float(r[i * 8 + 6]), __uint_as_float(r[i * 8 + 7]));
-          reinterpret_cast<uint4*>(dst + c * 32)[i] = u;
-        }
+        for (int i = 0; i < 32; ++i) cs[i] = __uint_as_float(rr[i]);
+        warp_colsum<32>(cs, lane);
+        atomicAdd(&sBias[which * AT_D + hf * 32 + lane], cs[0]);
       }
     }
   }
   tc_fence_before();
   __syncthreads();
+  if (P.dbias != nullptr && tid < 3 * AT_D) {
+    const int which = tid / AT_D, c = tid % AT_D;
+    atomicAdd(P.dbias + which * P.H + h * AT_D + c, sBias[tid]);
+  }
   if (warp == 0) {
     tc_fence_after();
-    tmem_dealloc(tmem, 512);
+    tmem_dealloc(tmem, 256);
   }
 }
 
-constexpr int ATTN_FWD_SMEM = 3 * TILE_BYTES + PBUF_BYTES + AT_S * 4 + 64 + 1024;
-constexpr int ATTN_BWD_SMEM = 4 * TILE_BYTES + 2 * PBUF_BYTES + AT_S * 4 + 64 + 1024;
+constexpr int ATTN_FWD_SMEM = 3 * TILE_BYTES + PBUF_BYTES + 3 * AT_S * 4 + 64 + 1024;
+constexpr int ATTN_BWD_SMEM = 4 * TILE_BYTES + PBUF_BYTES + AT_S * 4 + 3 * AT_D * 4 + 64 + 1024;
 
 static int attn_check(const char* who, int B, int S, int heads, int H) {
   if (S != AT_S || heads <= 0 || H != heads * AT_D || B <= 0) {
@@ -400,39 +445,42 @@ extern "C" int hs_attention_fwd(const void* qkv, const float* mask, void* ctx, f
   if (dropout_p > 0.f && seed == nullptr) { set_last_error("hs_attention_fwd: dropout needs a seed pointer"); return 1; }
   CUtensorMap tm;
   if (make_tmap_2d_16b(&tm, qkv, 3ull * H, static_cast<uint64_t>(B) * S, 3ull * H, 64, AT_S)) return 1;
-  AttnParams P{mask, ctx, nullptr, nullptr, lse, B, heads, H, 0.125f, dropout_p, seed, site};
+  AttnParams P{mask, ctx, nullptr, nullptr, lse, nullptr, B, heads, H, 0.125f, dropout_p, seed, site};
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const int grid = B * heads;
   if (dtype == HS_F16) {
     static bool done = false;
-    if (!done) { HS_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATTN_FWD_SMEM)); done = true; }
+    if (!done) { HS_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATTN_FWD_SMEM)); HS_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<__half>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared)); done = true; }
     attn_fwd_kernel<__half><<<grid, AT_THREADS, ATTN_FWD_SMEM, s>>>(tm, P);
   } else if (dtype == HS_BF16) {
     static bool done = false;
-    if (!done) { HS_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATTN_FWD_SMEM)); done = true; }
+    if (!done) { HS_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATTN_FWD_SMEM)); HS_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<__nv_bfloat16>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared)); done = true; }
     attn_fwd_kernel<__nv_bfloat16><<<grid, AT_THREADS, ATTN_FWD_SMEM, s>>>(tm, P);
   } else { set_last_error("hs_attention_fwd: dtype must be f16 or bf16"); return 1; }
   return post_launch("attn_fwd_kernel");
 }
 
 extern "C" int hs_attention_bwd(const void* qkv, const float* mask, const void* ctx, const void* dctx, const float* lse,
-                                void* dqkv, int B, int S, int heads, int H, float dropout_p, const long long* seed,
-                                unsigned site, int dtype, hs_stream_t stream) {
+                                void* dqkv, float* dbias, int accumulate_bias, int B, int S, int heads, int H,
+                                float dropout_p, const long long* seed, unsigned site, int dtype,
+                                hs_stream_t stream) {
   if (attn_check("hs_attention_bwd", B, S, heads, H)) return 1;
+  if (dbias != nullptr && !accumulate_bias)
+    HS_CUDA_OK(cudaMemsetAsync(dbias, 0, sizeof(float) * 3 * H, static_cast<cudaStream_t>(stream)));
   if (dropout_p > 0.f && seed == nullptr) { set_last_error("hs_attention_bwd: dropout needs a seed pointer"); return 1; }
   CUtensorMap tmQ, tmD;
   if (make_tmap_2d_16b(&tmQ, qkv, 3ull * H, static_cast<uint64_t>(B) * S, 3ull * H, 64, AT_S)) return 1;
   if (make_tmap_2d_16b(&tmD, dctx, static_cast<uint64_t>(H), static_cast<uint64_t>(B) * S, static_cast<uint64_t>(H), 64, AT_S)) return 1;
-  AttnParams P{mask, dqkv, ctx, dctx, const_cast<float*>(lse), B, heads, H, 0.125f, dropout_p, seed, site};
+  AttnParams P{mask, dqkv, ctx, dctx, const_cast<float*>(lse), dbias, B, heads, H, 0.125f, dropout_p, seed, site};
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const int grid = B * heads;
   if (dtype == HS_F16) {
     static bool done = false;
-    if (!done) { HS_CUDA_OK(cudaFuncSetAttribute(attn_bwd_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATTN_BWD_SMEM)); done = true; }
+    if (!done) { HS_CUDA_OK(cudaFuncSetAttribute(attn_bwd_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATTN_BWD_SMEM)); HS_CUDA_OK(cudaFuncSetAttribute(attn_bwd_kernel<__half>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared)); done = true; }
     attn_bwd_kernel<__half><<<grid, AT_THREADS, ATTN_BWD_SMEM, s>>>(tmQ, tmD, P);
   } else if (dtype == HS_BF16) {
     static bool done = false;
-    if (!done) { HS_CUDA_OK(cudaFuncSetAttribute(attn_bwd_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATTN_BWD_SMEM)); done = true; }
+    if (!done) { HS_CUDA_OK(cudaFuncSetAttribute(attn_bwd_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATTN_BWD_SMEM)); HS_CUDA_OK(cudaFuncSetAttribute(attn_bwd_kernel<__nv_bfloat16>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared)); done = true; }
     attn_bwd_kernel<__nv_bfloat16><<<grid, AT_THREADS, ATTN_BWD_SMEM, s>>>(tmQ, tmD, P);
   } else { set_last_error("hs_attention_bwd: dtype must be f16 or bf16"); return 1; }
   return post_launch("attn_bwd_kernel");

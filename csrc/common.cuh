@@ -116,6 +116,15 @@ __device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* t
       : "memory");
 }
 
+// Untiled bulk copy global -> shared (one contiguous run, 16-byte aligned, size % 16 == 0), completing on
+// an mbarrier like a tensor-map load: rows of an activation matrix straight into a per-warp ring.
+__device__ __forceinline__ void bulk_load_1d(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+      ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(gsrc)), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+
 // ----------------------------------------------------------------------------------------------
 // tcgen05 / TMEM
 // ----------------------------------------------------------------------------------------------
@@ -347,6 +356,24 @@ __device__ __forceinline__ float4 philox_uniform4(uint64_t seed, uint32_t stream
   return make_float4(r.x * s, r.y * s, r.z * s, r.w * s);
 }
 
+// Dropout keep/scale factors for the 8 consecutive elements of group `idx8` (= element index / 8) of logical
+// stream `stream`: ONE Philox call gives 128 bits = 8 x 16-bit uniforms; an element is dropped when its field
+// is below thr16 = round(p * 65536) (p is honoured to 1.5e-5). Forward and backward kernels call this with
+// the same arguments, so no mask is ever stored.
+__device__ __forceinline__ uint64_t philox_seed(const long long* seed_ptr) {
+  return static_cast<uint64_t>(seed_ptr[0]) * 0x9E3779B97F4A7C15ull + static_cast<uint64_t>(seed_ptr[1]);
+}
+__device__ __forceinline__ uint32_t dropout_thr16(float p) { return static_cast<uint32_t>(p * 65536.0f + 0.5f); }
+__device__ __forceinline__ void philox_keep8(uint64_t seed, uint32_t stream, uint64_t idx8, uint32_t thr16, float scale,
+                                             float (&mk)[8]) {
+  const uint4 r = philox4x32(static_cast<uint32_t>(idx8), static_cast<uint32_t>(idx8 >> 32), stream, 0u,
+                             static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32));
+  mk[0] = (r.x & 0xFFFFu) >= thr16 ? scale : 0.f; mk[1] = (r.x >> 16) >= thr16 ? scale : 0.f;
+  mk[2] = (r.y & 0xFFFFu) >= thr16 ? scale : 0.f; mk[3] = (r.y >> 16) >= thr16 ? scale : 0.f;
+  mk[4] = (r.z & 0xFFFFu) >= thr16 ? scale : 0.f; mk[5] = (r.z >> 16) >= thr16 ? scale : 0.f;
+  mk[6] = (r.w & 0xFFFFu) >= thr16 ? scale : 0.f; mk[7] = (r.w >> 16) >= thr16 ? scale : 0.f;
+}
+
 // ----------------------------------------------------------------------------------------------
 // reductions
 // ----------------------------------------------------------------------------------------------
@@ -359,6 +386,29 @@ __device__ __forceinline__ float warp_max(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
   return v;
+}
+
+// Column sums over the 32 lanes of a warp when every lane holds one ROW of N values (N = 32 * 2^k):
+// a halving butterfly -- at each step a lane keeps one half of its values and trades the other half with
+// its partner -- so N-32 + ... shuffles instead of 5*N. Afterwards v[0 .. N/32) of lane L hold the sums of
+// columns L*(N/32) .. L*(N/32) + N/32 - 1. Destroys v.
+template <int N>
+__device__ __forceinline__ void warp_colsum(float (&v)[N], int lane) {
+  static_assert(N >= 32 && (N & (N - 1)) == 0, "N must be a power of two >= 32");
+  int half = N / 2;
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) {
+    const bool up = (lane & off) != 0;
+#pragma unroll
+    for (int i = 0; i < N / 2; ++i) {
+      if (i < half) {
+        const float send = up ? v[i] : v[i + half];
+        const float keep = up ? v[i + half] : v[i];
+        v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+      }
+    }
+    half >>= 1;
+  }
 }
 
 }  // namespace hs

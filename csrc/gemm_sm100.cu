@@ -39,6 +39,7 @@ struct GemmParams {
   const void* bias;
   void* aux_out;
   const void* aux_in;
+  float* colsum_out;   // non-NULL: column sums of the produced C tile are atomically added here (bias gradient)
   int M, N, K, ldc, ldaux;
   int tiles_m, tiles_n, num_kb;
   int a_mn, b_mn;
@@ -272,12 +273,23 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
       const int tile = work % num_tiles, ks = work / num_tiles;
       const int tm = tile % p.tiles_m, tn = tile / p.tiles_m;
       const int n_base = tn * BN;
-      mbar_wait(&tfull_bar[as], aphase);
-      __syncwarp();
-      tc_fence_after();
       const int m0 = tm * TILE_M + cta_rank * BM + q * 32;
       const int m = m0 + lane;
       const bool row_ok = m < p.M;
+      // The epilogue operand (pre-activation for dGELU, residual-path gradient for ADD) is read row by row
+      // with per-thread loads; start pulling this warp's part of the tile towards L2 now, while the main loop
+      // of this tile is still running, so that those loads do not pay HBM latency later.
+      if (p.aux_in != nullptr && row_ok) {
+        const InT* arow = reinterpret_cast<const InT*>(p.aux_in) + static_cast<size_t>(m) * p.ldaux;
+#pragma unroll
+        for (int cc = 0; cc < (BN / 2) / CW; ++cc) {
+          const int n0 = n_base + half * (BN / 2) + cc * CW;
+          if (n0 < p.N) asm volatile("prefetch.global.L2 [%0];" ::"l"(arow + n0));
+        }
+      }
+      mbar_wait(&tfull_bar[as], aphase);
+      __syncwarp();
+      tc_fence_after();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
       const bool add_bias = bias != nullptr && ks == 0;
 #pragma unroll 1
@@ -357,6 +369,16 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
               for (int i = 0; i < 32; ++i) v[sub * 32 + i] *= gelu_grad_ref(x[i]);
             }
           }
+        } else if (p.act == HS_ACT_ADD_AUX) {
+          if (row_ok) {
+#pragma unroll
+            for (int sub = 0; sub < CW / 32; ++sub) {
+              float x[32];
+              load_row32<InT>(reinterpret_cast<const InT*>(p.aux_in) + static_cast<size_t>(m) * p.ldaux, n0 + sub * 32, p.N, vec, x);
+#pragma unroll
+              for (int i = 0; i < 32; ++i) v[sub * 32 + i] += x[i];
+            }
+          }
         }
         // ---- output
         if (tma) {
@@ -402,6 +424,20 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
               for (int i = 0; i < 32; ++i) t32[i] += o[i];
             }
             store_row32<OutT>(crow, n0 + sub * 32, p.N, vec, t32);
+          }
+        }
+        // ---- bias gradient of the Linear this tile is the output gradient of: column sums over the warp's
+        // 32 rows by a halving butterfly, then one RED per column
+        if (p.colsum_out != nullptr) {
+          if (!row_ok) {
+#pragma unroll
+            for (int i = 0; i < CW; ++i) v[i] = 0.f;
+          }
+          warp_colsum<CW>(v, lane);
+#pragma unroll
+          for (int i = 0; i < CW / 32; ++i) {
+            const int n = n0 + lane * (CW / 32) + i;
+            if (n < p.N) atomicAdd(p.colsum_out + n, v[i]);
           }
         }
       }
@@ -527,7 +563,7 @@ static int launch_gemm(const hs_gemm_args& a, cudaStream_t stream) {
   if (rc) return rc;
 
   GemmParams p;
-  p.C = a.C; p.bias = a.bias; p.aux_out = a.aux_out; p.aux_in = a.aux_in;
+  p.C = a.C; p.bias = a.bias; p.aux_out = a.aux_out; p.aux_in = a.aux_in; p.colsum_out = a.colsum_out;
   p.M = a.M; p.N = a.N; p.K = a.K; p.ldc = a.ldc; p.ldaux = a.ldaux;
   p.tiles_m = (a.M + TILE_M - 1) / TILE_M;
   p.tiles_n = (a.N + BN - 1) / BN;
@@ -550,15 +586,22 @@ static int launch_gemm(const hs_gemm_args& a, cudaStream_t stream) {
 
   const int tiles = p.tiles_m * p.tiles_n;
   const int sms = num_sms() / CG;   // workers: SMs, or SM pairs
-  // split-K: only with the reduce-add epilogue (C already holds a valid partial sum) and no per-column work
+  // split-K: only with the fp32 reduce-add epilogue and no per-column work. When the caller asked for
+  // overwrite semantics, C is cleared on the stream first and every split reduce-adds into it.
   p.split_k = 1;
-  if (p.tma_store && a.accumulate && a.bias == nullptr && a.act == HS_ACT_NONE && tiles < sms) {
+  if (vec && sizeof(OutT) == 4 && a.bias == nullptr && a.act == HS_ACT_NONE && a.colsum_out == nullptr && tiles < sms) {
     double best = 1e30;
     for (int s = 1; s <= 8 && s * 4 <= p.num_kb; ++s) {
       const int items = tiles * s;
       const int waves = (items + sms - 1) / sms;
       const double cost = waves * ((p.num_kb + s - 1) / s + 6.0);   // +6 k-blocks ~ prologue + epilogue of an item
       if (cost < best - 1e-9) { best = cost; p.split_k = s; }
+    }
+    if (p.split_k > 1 && !a.accumulate) {
+      HS_CUDA_OK(cudaMemset2DAsync(a.C, static_cast<size_t>(a.ldc) * sizeof(OutT), 0, static_cast<size_t>(a.N) * sizeof(OutT),
+                                   static_cast<size_t>(a.M), stream));
+      p.accumulate = 1;
+      p.tma_store = 1;
     }
   }
   p.kb_per_split = (p.num_kb + p.split_k - 1) / p.split_k;
@@ -571,6 +614,8 @@ static int launch_gemm(const hs_gemm_args& a, cudaStream_t stream) {
     if (make_tmap_2d(&tmC, a.C, a.N, a.M, a.ldc, CW, 32, sizeof(OutT))) return 1;
     if (a.aux_out != nullptr && make_tmap_2d(&tmAux, a.aux_out, a.N, a.M, a.ldaux, 64, 32, 2)) return 1;
   }
+  if (a.colsum_out != nullptr && !a.colsum_accumulate)
+    HS_CUDA_OK(cudaMemsetAsync(a.colsum_out, 0, sizeof(float) * a.N, stream));
   const int work = tiles * p.split_k;
   const int grid = (work < sms ? work : sms) * CG;
   kern<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, tmC, tmAux, p);
@@ -602,7 +647,7 @@ extern "C" int hs_gemm(const hs_gemm_args* args, hs_stream_t stream) {
     set_last_error("hs_gemm: A and B must be 16-byte aligned");
     return 1;
   }
-  if (a.act == HS_ACT_DGELU_MUL && a.aux_in == nullptr) { set_last_error("hs_gemm: DGELU_MUL needs aux_in"); return 1; }
+  if ((a.act == HS_ACT_DGELU_MUL || a.act == HS_ACT_ADD_AUX) && a.aux_in == nullptr) { set_last_error("hs_gemm: DGELU_MUL / ADD_AUX need aux_in"); return 1; }
   // Tile-width heuristic: prefer 128x256 tiles (fewer B re-reads) unless 128x128 fills the SMs better.
   const int sms = num_sms();
   const long tm = (a.M + BM - 1) / BM;

@@ -35,18 +35,6 @@ __device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
   return u;
 }
 
-// keep/scale factors for the 8 consecutive elements starting at flat element index e0 (e0 % 8 == 0)
-__device__ __forceinline__ void dropout_mask8(const long long* seed_ptr, uint32_t site, uint64_t e0, float p,
-                                              float scale, float (&mk)[8]) {
-  const uint64_t seed = static_cast<uint64_t>(seed_ptr[0]) * 0x9E3779B97F4A7C15ull + static_cast<uint64_t>(seed_ptr[1]);
-  const float4 r0 = philox_uniform4(seed, site, e0 >> 2);
-  const float4 r1 = philox_uniform4(seed, site, (e0 >> 2) + 1);
-  mk[0] = r0.x >= p ? scale : 0.f; mk[1] = r0.y >= p ? scale : 0.f;
-  mk[2] = r0.z >= p ? scale : 0.f; mk[3] = r0.w >= p ? scale : 0.f;
-  mk[4] = r1.x >= p ? scale : 0.f; mk[5] = r1.y >= p ? scale : 0.f;
-  mk[6] = r1.z >= p ? scale : 0.f; mk[7] = r1.w >= p ? scale : 0.f;
-}
-
 struct LnFwdParams {
   const void* x; const void* bias; const void* residual; const void* gamma; const void* beta;
   void* y; void* z; float* mean; float* rstd;
@@ -64,6 +52,8 @@ __global__ void __launch_bounds__(LN_THREADS) ln_fwd_kernel(LnFwdParams P) {
   const T* res = P.residual ? reinterpret_cast<const T*>(P.residual) + static_cast<size_t>(row) * P.H : nullptr;
   const bool drop = P.p > 0.f;
   const float scale = drop ? 1.f / (1.f - P.p) : 1.f;
+  const uint64_t seed = drop ? philox_seed(P.seed) : 0ull;
+  const uint32_t thr = dropout_thr16(P.p);
   float v[NV][8];
   float sum = 0.f;
 #pragma unroll
@@ -80,7 +70,7 @@ __global__ void __launch_bounds__(LN_THREADS) ln_fwd_kernel(LnFwdParams P) {
       }
       if (drop && !P.post_dropout) {
         float mk[8];
-        dropout_mask8(P.seed, P.site, static_cast<uint64_t>(row) * P.H + vi * 8, P.p, scale, mk);
+        philox_keep8(seed, P.site, (static_cast<uint64_t>(row) * P.H + vi * 8) >> 3, thr, scale, mk);
 #pragma unroll
         for (int k = 0; k < 8; ++k) f[k] *= mk[k];
       }
@@ -121,7 +111,7 @@ __global__ void __launch_bounds__(LN_THREADS) ln_fwd_kernel(LnFwdParams P) {
       for (int k = 0; k < 8; ++k) o[k] = g[k] * ((v[j][k] - mean) * rstd) + b[k];
       if (drop && P.post_dropout) {
         float mk[8];
-        dropout_mask8(P.seed, P.site, static_cast<uint64_t>(row) * P.H + vi * 8, P.p, scale, mk);
+        philox_keep8(seed, P.site, (static_cast<uint64_t>(row) * P.H + vi * 8) >> 3, thr, scale, mk);
 #pragma unroll
         for (int k = 0; k < 8; ++k) o[k] *= mk[k];
       }
@@ -135,30 +125,66 @@ struct LnBwdParams {
   void* dz;       // gradient w.r.t. z (the residual path), 16-bit
   void* dx;       // gradient w.r.t. x = dz * dropout mask (NULL when p == 0 and dz suffices)
   float* dgamma; float* dbeta;             // fp32 destinations, accumulated with one atomicAdd per block and column
+  float* dbias;   // optional fp32 [H]: column sums of dx -- the bias gradient of the Linear that produced x
   int M, H; float p; const long long* seed; uint32_t site;
   int post_dropout;  // 1: dy is first multiplied by the mask (embeddings: y = dropout(LN(z)))
-  int rows_per_block;
 };
 
-template <typename T, int NV>
-__global__ void __launch_bounds__(LN_THREADS) ln_bwd_kernel(LnBwdParams P) {
-  extern __shared__ float sm[];  // [LN_ROWS_PER_BLOCK][2][H] warp-private partials
+constexpr int LNB_WARPS = 8;
+constexpr int LNB_THREADS = LNB_WARPS * 32;
+
+// Persistent: one CTA per SM, one warp per row at a time. Each warp owns a LNB_STAGES-deep ring of
+// (dy row, z row) pairs in shared memory that lane 0 fills with untiled bulk copies (cp.async.bulk +
+// mbarrier complete_tx), so up to 4 rows x 8 warps x 4 KB = 128 KB of loads are in flight per SM without
+// holding a single register; the per-column partials (dgamma, dbeta and the bias gradient) stay in
+// registers across all rows of the warp and meet in shared memory (the retired ring) at the end.
+template <typename T, int NV, int LNB_STAGES>
+__global__ void __launch_bounds__(LNB_THREADS, 1) ln_bwd_kernel(LnBwdParams P, uint32_t bar_offset) {
+  extern __shared__ __align__(128) uint8_t lnb_smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nvec = P.H >> 3;
+  const uint32_t row_bytes = static_cast<uint32_t>(P.H) * sizeof(T);
+  uint8_t* ring = lnb_smem + static_cast<size_t>(warp) * LNB_STAGES * 2 * row_bytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(lnb_smem + bar_offset) + warp * LNB_STAGES;
   const bool drop = P.p > 0.f;
   const float scale = drop ? 1.f / (1.f - P.p) : 1.f;
-  float dg[NV][8], db[NV][8];
-#pragma unroll
-  for (int j = 0; j < NV; ++j)
-#pragma unroll
-    for (int k = 0; k < 8; ++k) { dg[j][k] = 0.f; db[j][k] = 0.f; }
+  const uint64_t seed = drop ? philox_seed(P.seed) : 0ull;
+  const uint32_t thr = dropout_thr16(P.p);
+  const int gw = blockIdx.x * LNB_WARPS + warp, GW = gridDim.x * LNB_WARPS;
 
-  const int row0 = blockIdx.x * P.rows_per_block;
-  const int row_end = min(P.M, row0 + P.rows_per_block);
-  for (int row = row0 + warp; row < row_end; row += LN_ROWS_PER_BLOCK) {
-    const T* dy = reinterpret_cast<const T*>(P.dy) + static_cast<size_t>(row) * P.H;
-    const T* z = reinterpret_cast<const T*>(P.z) + static_cast<size_t>(row) * P.H;
+  if (lane == 0) {
+#pragma unroll
+    for (int s = 0; s < LNB_STAGES; ++s) mbar_init(&bars[s], 1);
+    fence_mbar_init();
+#pragma unroll
+    for (int s = 0; s < LNB_STAGES; ++s) {
+      const long long row = gw + static_cast<long long>(s) * GW;
+      if (row < P.M) {
+        mbar_expect_tx(&bars[s], 2 * row_bytes);
+        bulk_load_1d(ring + (2 * s) * row_bytes, reinterpret_cast<const T*>(P.dy) + row * P.H, row_bytes, &bars[s]);
+        bulk_load_1d(ring + (2 * s + 1) * row_bytes, reinterpret_cast<const T*>(P.z) + row * P.H, row_bytes, &bars[s]);
+      }
+    }
+  }
+  __syncwarp();
+
+  float dg[NV][8], db[NV][8], dc[NV][8];
+  uint4 gpk[NV];
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { dg[j][k] = 0.f; db[j][k] = 0.f; dc[j][k] = 0.f; }
+    const int vi = j * 32 + lane;
+    gpk[j] = vi < nvec ? reinterpret_cast<const uint4*>(P.gamma)[vi] : make_uint4(0, 0, 0, 0);
+  }
+
+  int stage = 0;
+  uint32_t phase = 0;
+  for (long long row = gw; row < P.M; row += GW) {
     const float mean = P.mean[row], rstd = P.rstd[row];
+    mbar_wait(&bars[stage], phase);
+    const uint4* sdy = reinterpret_cast<const uint4*>(ring + (2 * stage) * row_bytes);
+    const uint4* sz = reinterpret_cast<const uint4*>(ring + (2 * stage + 1) * row_bytes);
     float xh[NV][8], gy[NV][8];
     float s1 = 0.f, s2 = 0.f;
 #pragma unroll
@@ -166,12 +192,12 @@ __global__ void __launch_bounds__(LN_THREADS) ln_bwd_kernel(LnBwdParams P) {
       const int vi = j * 32 + lane;
       if (vi < nvec) {
         float d[8], zz[8], g[8];
-        unpack8<T>(reinterpret_cast<const uint4*>(dy)[vi], d);
-        unpack8<T>(reinterpret_cast<const uint4*>(z)[vi], zz);
-        unpack8<T>(reinterpret_cast<const uint4*>(P.gamma)[vi], g);
+        unpack8<T>(sdy[vi], d);
+        unpack8<T>(sz[vi], zz);
+        unpack8<T>(gpk[j], g);
         if (drop && P.post_dropout) {
           float mk[8];
-          dropout_mask8(P.seed, P.site, static_cast<uint64_t>(row) * P.H + vi * 8, P.p, scale, mk);
+          philox_keep8(seed, P.site, (static_cast<uint64_t>(row) * P.H + vi * 8) >> 3, thr, scale, mk);
 #pragma unroll
           for (int k = 0; k < 8; ++k) d[k] *= mk[k];
         }
@@ -188,6 +214,17 @@ __global__ void __launch_bounds__(LN_THREADS) ln_bwd_kernel(LnBwdParams P) {
         }
       }
     }
+    // the ring slot is consumed: refill it with the row LNB_STAGES rounds ahead
+    __syncwarp();
+    if (lane == 0) {
+      const long long nxt = row + static_cast<long long>(LNB_STAGES) * GW;
+      if (nxt < P.M) {
+        mbar_expect_tx(&bars[stage], 2 * row_bytes);
+        bulk_load_1d(ring + (2 * stage) * row_bytes, reinterpret_cast<const T*>(P.dy) + nxt * P.H, row_bytes, &bars[stage]);
+        bulk_load_1d(ring + (2 * stage + 1) * row_bytes, reinterpret_cast<const T*>(P.z) + nxt * P.H, row_bytes, &bars[stage]);
+      }
+    }
+    if (++stage == LNB_STAGES) { stage = 0; phase ^= 1; }
     s1 = warp_sum(s1) / P.H;
     s2 = warp_sum(s2) / P.H;
     T* dz = reinterpret_cast<T*>(P.dz) + static_cast<size_t>(row) * P.H;
@@ -203,36 +240,49 @@ __global__ void __launch_bounds__(LN_THREADS) ln_bwd_kernel(LnBwdParams P) {
         if (dx) {
           if (drop && !P.post_dropout) {
             float mk[8];
-            dropout_mask8(P.seed, P.site, static_cast<uint64_t>(row) * P.H + vi * 8, P.p, scale, mk);
+            philox_keep8(seed, P.site, (static_cast<uint64_t>(row) * P.H + vi * 8) >> 3, thr, scale, mk);
 #pragma unroll
             for (int k = 0; k < 8; ++k) o[k] *= mk[k];
           }
           reinterpret_cast<uint4*>(dx)[vi] = pack8<T>(o);
         }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) dc[j][k] += o[k];
       }
     }
   }
-  // combine the 4 warps' gamma/beta partials through shared memory, one partial row per block
-  float* sg = sm + static_cast<size_t>(warp) * 2 * P.H;
-  float* sb = sg + P.H;
+
+  // combine the warps' per-column partials through shared memory (the ring is retired: every bulk copy this
+  // warp issued has been waited for), then one atomicAdd per block and column
+  __syncthreads();
+  float* sm = reinterpret_cast<float*>(lnb_smem);
+  const int narr = P.dbias ? 3 : 2;
+  float* mine = sm + static_cast<size_t>(warp) * narr * P.H;
 #pragma unroll
   for (int j = 0; j < NV; ++j) {
     const int vi = j * 32 + lane;
     if (vi < nvec) {
-#pragma unroll
-      for (int k = 0; k < 8; ++k) { sg[vi * 8 + k] = dg[j][k]; sb[vi * 8 + k] = db[j][k]; }
+      float4* a = reinterpret_cast<float4*>(mine + vi * 8);
+      a[0] = make_float4(dg[j][0], dg[j][1], dg[j][2], dg[j][3]);
+      a[1] = make_float4(dg[j][4], dg[j][5], dg[j][6], dg[j][7]);
+      float4* b = reinterpret_cast<float4*>(mine + P.H + vi * 8);
+      b[0] = make_float4(db[j][0], db[j][1], db[j][2], db[j][3]);
+      b[1] = make_float4(db[j][4], db[j][5], db[j][6], db[j][7]);
+      if (P.dbias) {
+        float4* c = reinterpret_cast<float4*>(mine + 2 * P.H + vi * 8);
+        c[0] = make_float4(dc[j][0], dc[j][1], dc[j][2], dc[j][3]);
+        c[1] = make_float4(dc[j][4], dc[j][5], dc[j][6], dc[j][7]);
+      }
     }
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < P.H; i += blockDim.x) {
-    float a = 0.f, b = 0.f;
+  for (int i = threadIdx.x; i < narr * P.H; i += blockDim.x) {
+    float a = 0.f;
 #pragma unroll
-    for (int w = 0; w < LN_ROWS_PER_BLOCK; ++w) {
-      a += sm[static_cast<size_t>(w) * 2 * P.H + i];
-      b += sm[static_cast<size_t>(w) * 2 * P.H + P.H + i];
-    }
-    if (P.dgamma) atomicAdd(P.dgamma + i, a);
-    if (P.dbeta) atomicAdd(P.dbeta + i, b);
+    for (int w = 0; w < LNB_WARPS; ++w) a += sm[static_cast<size_t>(w) * narr * P.H + i];
+    const int arr = i / P.H, col = i - arr * P.H;
+    float* dst = arr == 0 ? P.dgamma : (arr == 1 ? P.dbeta : P.dbias);
+    if (dst) atomicAdd(dst + col, a);
   }
 }
 
@@ -305,34 +355,55 @@ extern "C" int hs_ln_fwd(const void* x, const void* bias, const void* residual, 
 
 extern "C" int hs_ln_bwd(const void* dy, const void* z, const void* gamma, const float* mean, const float* rstd,
                          void* dz, void* dx, float* dgamma, float* dbeta, int accumulate_params,
+                         float* dbias, int accumulate_bias,
                          int M, int H, float dropout_p, const long long* seed, unsigned site, int post_dropout,
                          int dtype, hs_stream_t stream) {
   if (ln_check("hs_ln_bwd", M, H)) return 1;
-  const int blocks = num_sms() * 2;
-  const int rpb = (M + blocks - 1) / blocks;
-  const int rows_per_block = ((rpb + LN_ROWS_PER_BLOCK - 1) / LN_ROWS_PER_BLOCK) * LN_ROWS_PER_BLOCK;
-  const int grid = (M + rows_per_block - 1) / rows_per_block;
-  cudaStream_t s0 = static_cast<cudaStream_t>(stream);
-  if (!accumulate_params) {   // overwrite semantics: clear the destinations, then accumulate into them
-    if (dgamma) HS_CUDA_OK(cudaMemsetAsync(dgamma, 0, sizeof(float) * H, s0));
-    if (dbeta) HS_CUDA_OK(cudaMemsetAsync(dbeta, 0, sizeof(float) * H, s0));
+  if (dropout_p > 0.f && seed == nullptr) { set_last_error("hs_ln_bwd: dropout needs a seed pointer"); return 1; }
+  if ((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(z)) % 16) {
+    set_last_error("hs_ln_bwd: dy and z must be 16-byte aligned");
+    return 1;
   }
-  LnBwdParams P{dy, z, gamma, mean, rstd, dz, dx, dgamma, dbeta, M, H, dropout_p, seed, site, post_dropout, rows_per_block};
-  const size_t smem = static_cast<size_t>(LN_ROWS_PER_BLOCK) * 2 * H * sizeof(float);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  if (smem > 48 * 1024) { set_last_error("hs_ln_bwd: H=%d needs %zu B of shared memory", H, smem); return 1; }
+  if (!accumulate_params) {   // overwrite semantics: clear the destinations, then accumulate into them
+    if (dgamma) HS_CUDA_OK(cudaMemsetAsync(dgamma, 0, sizeof(float) * H, s));
+    if (dbeta) HS_CUDA_OK(cudaMemsetAsync(dbeta, 0, sizeof(float) * H, s));
+  }
+  if (dbias && !accumulate_bias) HS_CUDA_OK(cudaMemsetAsync(dbias, 0, sizeof(float) * H, s));
+  LnBwdParams P{dy, z, gamma, mean, rstd, dz, dx, dgamma, dbeta, dbias, M, H, dropout_p, seed, site, post_dropout};
   const int nv = (H + 255) / 256;
-#define HS_LN_BWD(T)                                                                    \
-  do {                                                                                  \
-    if (nv <= 1) ln_bwd_kernel<T, 1><<<grid, LN_THREADS, smem, s>>>(P);                 \
-    else if (nv <= 2) ln_bwd_kernel<T, 2><<<grid, LN_THREADS, smem, s>>>(P);            \
-    else if (nv <= 4) ln_bwd_kernel<T, 4><<<grid, LN_THREADS, smem, s>>>(P);            \
-    else ln_bwd_kernel<T, 8><<<grid, LN_THREADS, smem, s>>>(P);                         \
+  const int stages = nv <= 4 ? 4 : 2;     // rows in flight per warp; H = 2048 leaves room for two
+  const size_t esz = 2;
+  const size_t ring = static_cast<size_t>(LNB_WARPS) * stages * 2 * H * esz;
+  const size_t red = static_cast<size_t>(LNB_WARPS) * 3 * H * sizeof(float);
+  const size_t bar_offset = ring > red ? ring : red;
+  const size_t smem = bar_offset + LNB_WARPS * stages * sizeof(uint64_t);
+  if (smem > 227 * 1024) { set_last_error("hs_ln_bwd: H=%d needs %zu B of shared memory", H, smem); return 1; }
+  const int rows_blocks = (M + LNB_WARPS - 1) / LNB_WARPS;
+  const int grid = rows_blocks < num_sms() ? rows_blocks : num_sms();
+#define HS_LN_BWD_ONE(T, NVV, ST)                                                                        \
+  do {                                                                                                 \
+    static bool attr_done[64] = {false};                                                               \
+    int dev = 0;                                                                                       \
+    HS_CUDA_OK(cudaGetDevice(&dev));                                                                   \
+    if (dev < 64 && !attr_done[dev]) {                                                                 \
+      HS_CUDA_OK(cudaFuncSetAttribute(ln_bwd_kernel<T, NVV, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024)); \
+      attr_done[dev] = true;                                                                           \
+    }                                                                                                  \
+    ln_bwd_kernel<T, NVV, ST><<<grid, LNB_THREADS, smem, s>>>(P, static_cast<uint32_t>(bar_offset));                                    \
+  } while (0)
+#define HS_LN_BWD(T)                                  \
+  do {                                                \
+    if (nv <= 1) HS_LN_BWD_ONE(T, 1, 4);              \
+    else if (nv <= 2) HS_LN_BWD_ONE(T, 2, 4);         \
+    else if (nv <= 4) HS_LN_BWD_ONE(T, 4, 4);         \
+    else HS_LN_BWD_ONE(T, 8, 2);                      \
   } while (0)
   if (dtype == HS_F16) HS_LN_BWD(__half);
   else if (dtype == HS_BF16) HS_LN_BWD(__nv_bfloat16);
   else { set_last_error("hs_ln_bwd: dtype must be f16 or bf16"); return 1; }
 #undef HS_LN_BWD
+#undef HS_LN_BWD_ONE
   return post_launch("ln_bwd_kernel");
 }
 

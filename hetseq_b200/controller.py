@@ -375,6 +375,7 @@ class Controller(object):
                 loss_sum = loss_sum + logging_output['loss'].float() * weight
         if marks is not None:
             marks.append(self._mark())      # forward + backward enqueued
+        opt.buffer.finalize_grads()
         dp.finish_gradients(opt)
         if marks is not None:
             marks.append(self._mark())      # gradient reduction complete

@@ -35,7 +35,7 @@ class AttentionFn(torch.autograd.Function):
         dqkv = torch.empty_like(qkv)
         seed = rng.seed_tensor(qkv.device) if p > 0 else None
         lib.check(L.hs_attention_bwd(qkv.data_ptr(), add_mask.data_ptr(), out.data_ptr(), dout.data_ptr(), lse.data_ptr(),
-                                     dqkv.data_ptr(), B, S, heads, H, float(p), lib.ptr(seed), int(site),
+                                     dqkv.data_ptr(), None, 0, B, S, heads, H, float(p), lib.ptr(seed), int(site),
                                      lib.dtype_code(qkv.dtype), lib.stream_ptr()), 'hs_attention_bwd')
         return dqkv, None, None, None, None, None, None
 

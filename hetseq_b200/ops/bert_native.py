@@ -21,13 +21,14 @@ Activations are 16-bit (fp16 or bf16), accumulation fp32. Dropout masks are neve
 from __future__ import annotations
 
 import math
+import os
 from typing import Optional
 
 import torch
 import torch.nn.functional as F
 
-from hetseq_b200.ops import native, rng
-from hetseq_b200.ops.native import ACT_DGELU_MUL, ACT_GELU, ACT_NONE, ACT_TANH
+from hetseq_b200.ops import lib, native, rng
+from hetseq_b200.ops.native import ACT_ADD_AUX, ACT_DGELU_MUL, ACT_GELU, ACT_NONE, ACT_TANH
 
 
 def _flat(p):
@@ -185,6 +186,123 @@ def drop_add_ln(x, residual, ln_module, p, site, post=False):
 
 
 # ------------------------------------------------------------------------------------------------
+# one autograd node per encoder layer
+# ------------------------------------------------------------------------------------------------
+class EncoderLayerFn(torch.autograd.Function):
+    """A whole BertLayer (bert_modeling.py:351-437) as ONE autograd node with a hand-scheduled backward.
+
+    forward : QKV GEMM -> fused attention -> out-proj GEMM -> dropout+residual+LN -> FFN1 GEMM(+GELU) ->
+              FFN2 GEMM -> dropout+residual+LN                                  (7 launches)
+    backward: LN bwd (+ FFN2 bias grad) -> FFN2 dgrad (x GELU', + FFN1 bias grad in the epilogue), FFN2 wgrad
+              -> FFN1 dgrad (+ residual-path gradient in the epilogue), FFN1 wgrad -> LN bwd (+ out-proj bias
+              grad) -> out-proj dgrad, wgrad -> attention bwd (+ q/k/v bias grad) -> QKV dgrad (+ residual-path
+              gradient), QKV wgrad                                            (11 launches)
+    Compared with one node per op this removes the four bias-gradient reductions and the two gradient
+    additions autograd inserts where the residual stream forks. Gradients go straight into the flat fp32
+    buffer; each parameter is reported ready as soon as its gradient is final (bucket overlap)."""
+
+    @staticmethod
+    def forward(ctx, x, add_mask, anchor, nb, layer, training):
+        L = lib.load()
+        B, S = nb._bs
+        H, I, heads = nb.H, nb.I, nb.heads
+        M = x.shape[0]
+        dt, dev = x.dtype, x.device
+        qkv_w, qkv_b, ws, bs = nb.packed[id(layer)]
+        so, inter, out = layer.attention.output, layer.intermediate.dense_act, layer.output
+        p_attn = nb.p_attn if training else 0.0
+        p_h = nb.p_hidden if training else 0.0
+        seed = rng.seed_tensor(dev) if (p_attn > 0 or p_h > 0) else None
+        s_attn, s_ao, s_ffn = (nb.sites[(id(layer), t)] for t in ('attn', 'ao', 'ffn'))
+
+        qkv = torch.empty(M, 3 * H, dtype=dt, device=dev)
+        native.gemm(x, qkv_w, qkv, M, 3 * H, H, lda=H, ldb=H, ldc=3 * H, bias=qkv_b)
+        ctxv = torch.empty(M, H, dtype=dt, device=dev)
+        lse = torch.empty(B * heads * S, dtype=torch.float32, device=dev)
+        lib.check(L.hs_attention_fwd(qkv.data_ptr(), add_mask.data_ptr(), ctxv.data_ptr(), lse.data_ptr(), B, S, heads, H,
+                                     float(p_attn), lib.ptr(seed), int(s_attn), lib.dtype_code(dt), lib.stream_ptr()),
+                  'hs_attention_fwd')
+        ao = torch.empty(M, H, dtype=dt, device=dev)
+        native.gemm(ctxv, so.dense.weight, ao, M, H, H, lda=H, ldb=H, ldc=H, bias=so.dense.bias)
+        x1, z1, mean1, rstd1 = native.ln_fwd(ao, None, x, so.LayerNorm.weight, so.LayerNorm.bias, eps=1e-12, p=p_h,
+                                             seed=seed, site=s_ao)
+        del ao
+        pre = torch.empty(M, I, dtype=dt, device=dev)
+        h = torch.empty(M, I, dtype=dt, device=dev)
+        native.gemm(x1, inter.weight, h, M, I, H, lda=H, ldb=H, ldc=I, bias=inter.bias, act=ACT_GELU, aux_out=pre, ldaux=I)
+        f = torch.empty(M, H, dtype=dt, device=dev)
+        native.gemm(h, out.dense.weight, f, M, H, I, lda=I, ldb=I, ldc=H, bias=out.dense.bias)
+        x2, z2, mean2, rstd2 = native.ln_fwd(f, None, x1, out.LayerNorm.weight, out.LayerNorm.bias, eps=1e-12, p=p_h,
+                                             seed=seed, site=s_ffn)
+        del f
+        ctx.save_for_backward(x, add_mask, qkv, ctxv, lse, z1, mean1, rstd1, x1, pre, h, z2, mean2, rstd2)
+        ctx.meta = (nb, layer, p_attn, p_h, B, S)
+        return x2
+
+    @staticmethod
+    def backward(ctx, dx2):
+        x, add_mask, qkv, ctxv, lse, z1, mean1, rstd1, x1, pre, h, z2, mean2, rstd2 = ctx.saved_tensors
+        nb, layer, p_attn, p_h, B, S = ctx.meta
+        L = lib.load()
+        H, I, heads = nb.H, nb.I, nb.heads
+        M = x.shape[0]
+        dt, dev = x.dtype, x.device
+        qkv_w, qkv_b, ws, bs = nb.packed[id(layer)]
+        so, inter, out = layer.attention.output, layer.intermediate.dense_act, layer.output
+        seed = rng.seed_tensor(dev) if (p_attn > 0 or p_h > 0) else None
+        s_attn, s_ao, s_ffn = (nb.sites[(id(layer), t)] for t in ('attn', 'ao', 'ffn'))
+
+        # ---- output LayerNorm: dz2 feeds the residual path, df the FFN; FFN2's bias gradient rides along
+        gg, gacc = _wgrad_target([out.LayerNorm.weight])
+        bg, bacc = _wgrad_target([out.LayerNorm.bias])
+        b2g, b2acc = _wgrad_target([out.dense.bias])
+        dz2, df = native.ln_bwd(dx2.contiguous(), z2, out.LayerNorm.weight, mean2, rstd2, gg, bg, gacc, p=p_h,
+                                seed=seed, site=s_ffn, dbias=b2g, accumulate_bias=b2acc)
+        assert gacc == bacc
+        _notify([out.LayerNorm.weight, out.LayerNorm.bias, out.dense.bias])
+        # ---- FFN
+        b1g, b1acc = _wgrad_target([inter.bias])
+        dpre = torch.empty(M, I, dtype=dt, device=dev)
+        native.gemm(df, out.dense.weight, dpre, M, I, H, lda=H, ldb=I, ldc=I, b_mn=True, act=ACT_DGELU_MUL, aux_in=pre,
+                    ldaux=I, colsum_out=b1g, colsum_accumulate=b1acc)
+        wg2, acc2 = _wgrad_target([out.dense.weight])
+        native.gemm(df, h, wg2, H, I, M, lda=H, ldb=I, ldc=I, a_mn=True, b_mn=True, accumulate=acc2)
+        _notify([out.dense.weight, inter.bias])
+        dx1 = torch.empty(M, H, dtype=dt, device=dev)
+        native.gemm(dpre, inter.weight, dx1, M, H, I, lda=I, ldb=H, ldc=H, b_mn=True, act=ACT_ADD_AUX, aux_in=dz2, ldaux=H)
+        wg1, acc1 = _wgrad_target([inter.weight])
+        native.gemm(dpre, x1, wg1, I, H, M, lda=I, ldb=H, ldc=H, a_mn=True, b_mn=True, accumulate=acc1)
+        _notify([inter.weight])
+        del dpre, dz2, df
+        # ---- attention-output LayerNorm (+ out-proj bias gradient)
+        gg, gacc = _wgrad_target([so.LayerNorm.weight])
+        bg, bacc = _wgrad_target([so.LayerNorm.bias])
+        bog, boacc = _wgrad_target([so.dense.bias])
+        dz1, dao = native.ln_bwd(dx1, z1, so.LayerNorm.weight, mean1, rstd1, gg, bg, gacc, p=p_h, seed=seed,
+                                 site=s_ao, dbias=bog, accumulate_bias=boacc)
+        assert gacc == bacc
+        _notify([so.LayerNorm.weight, so.LayerNorm.bias, so.dense.bias])
+        dctx = torch.empty(M, H, dtype=dt, device=dev)
+        native.gemm(dao, so.dense.weight, dctx, M, H, H, lda=H, ldb=H, ldc=H, b_mn=True)
+        wgo, acco = _wgrad_target([so.dense.weight])
+        native.gemm(dao, ctxv, wgo, H, H, M, lda=H, ldb=H, ldc=H, a_mn=True, b_mn=True, accumulate=acco)
+        _notify([so.dense.weight])
+        # ---- attention (+ q/k/v bias gradient)
+        dqkv = torch.empty(M, 3 * H, dtype=dt, device=dev)
+        bqg, bqacc = _wgrad_target(bs)
+        lib.check(L.hs_attention_bwd(qkv.data_ptr(), add_mask.data_ptr(), ctxv.data_ptr(), dctx.data_ptr(), lse.data_ptr(),
+                                     dqkv.data_ptr(), bqg.data_ptr(), int(bqacc), B, S, heads, H, float(p_attn),
+                                     lib.ptr(seed), int(s_attn), lib.dtype_code(dt), lib.stream_ptr()), 'hs_attention_bwd')
+        _notify(bs)
+        dx = torch.empty(M, H, dtype=dt, device=dev)
+        native.gemm(dqkv, qkv_w, dx, M, H, 3 * H, lda=3 * H, ldb=H, ldc=H, b_mn=True, act=ACT_ADD_AUX, aux_in=dz1, ldaux=H)
+        wgq, accq = _wgrad_target(ws)
+        native.gemm(dqkv, x, wgq, 3 * H, H, M, lda=3 * H, ldb=H, ldc=H, a_mn=True, b_mn=True, accumulate=accq)
+        _notify(ws)
+        return dx, None, None, None, None, None
+
+
+# ------------------------------------------------------------------------------------------------
 # embeddings
 # ------------------------------------------------------------------------------------------------
 class EmbeddingSumFn(torch.autograd.Function):
@@ -313,6 +431,8 @@ class NativeBert(object):
         self.p_hidden = float(cfg.hidden_dropout_prob)
         self.p_attn = float(cfg.attention_probs_dropout_prob)
         self.sites = {}
+        # one autograd node per encoder layer (EncoderLayerFn); HETSEQ_FUSED_LAYER=0 keeps one node per op
+        self.fused_layer = os.environ.get('HETSEQ_FUSED_LAYER', '1') != '0'
         self.attn_impl = None
         try:
             from hetseq_b200.ops import attention_native
@@ -356,6 +476,11 @@ class NativeBert(object):
         x2 = x.reshape(B * S, H)
         training = layer.training
         qkv_w, qkv_b, ws, bs = self.packed[id(layer)]
+        if self.fused_layer and self.attn_impl is not None and \
+                self.attn_impl.supports(B, S, self.heads, H // self.heads, x2.dtype):
+            y = EncoderLayerFn.apply(x2.contiguous(), add_mask.contiguous(), layer.output.LayerNorm.weight, self, layer,
+                                     training)
+            return y.view(x.shape)
         qkv = linear(x2, qkv_w, qkv_b, ws, bs)
         p_attn = self.p_attn if training else 0.0
         if self.attn_impl is not None and self.attn_impl.supports(B, S, self.heads, H // self.heads, qkv.dtype):

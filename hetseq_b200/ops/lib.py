@@ -15,7 +15,7 @@ import torch
 _lib: Optional[ctypes.CDLL] = None
 
 HS_F16, HS_BF16, HS_F32 = 0, 1, 2
-ACT_NONE, ACT_GELU, ACT_TANH, ACT_DGELU_MUL = 0, 1, 2, 3
+ACT_NONE, ACT_GELU, ACT_TANH, ACT_DGELU_MUL, ACT_ADD_AUX = 0, 1, 2, 3, 4
 
 _DT = {torch.float16: HS_F16, torch.bfloat16: HS_BF16, torch.float32: HS_F32}
 
@@ -37,6 +37,7 @@ class GemmArgs(ctypes.Structure):
         ('bias', ctypes.c_void_p), ('act', ctypes.c_int),
         ('aux_out', ctypes.c_void_p), ('aux_in', ctypes.c_void_p), ('ldaux', ctypes.c_int),
         ('accumulate', ctypes.c_int), ('alpha', ctypes.c_float), ('alpha_dev', ctypes.c_void_p),
+        ('colsum_out', ctypes.c_void_p), ('colsum_accumulate', ctypes.c_int),
     ]
 
 

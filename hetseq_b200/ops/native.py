@@ -11,7 +11,7 @@ from typing import Optional
 import torch
 
 from hetseq_b200.ops import lib
-from hetseq_b200.ops.lib import ACT_DGELU_MUL, ACT_GELU, ACT_NONE, ACT_TANH  # noqa: F401
+from hetseq_b200.ops.lib import ACT_ADD_AUX, ACT_DGELU_MUL, ACT_GELU, ACT_NONE, ACT_TANH  # noqa: F401
 
 _scratch = {}
 
@@ -30,7 +30,8 @@ def scratch(device, n_floats: int, tag: str = 'default') -> torch.Tensor:
 def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, M: int, N: int, K: int, *, lda: int, ldb: int,
          ldc: int, a_mn: bool = False, b_mn: bool = False, bias: Optional[torch.Tensor] = None, act: int = ACT_NONE,
          aux_out: Optional[torch.Tensor] = None, aux_in: Optional[torch.Tensor] = None, ldaux: int = 0,
-         accumulate: bool = False, alpha: float = 1.0, alpha_dev: Optional[torch.Tensor] = None) -> torch.Tensor:
+         accumulate: bool = False, alpha: float = 1.0, alpha_dev: Optional[torch.Tensor] = None,
+         colsum_out: Optional[torch.Tensor] = None, colsum_accumulate: bool = False) -> torch.Tensor:
     """out[M,N] = epilogue(alpha * A(m,k) B(n,k)); see include/hetseq_b200.h for operand layouts."""
     L = lib.load()
     g = lib.GemmArgs()
@@ -46,6 +47,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, M: int, N: int, K:
     g.accumulate = int(accumulate)
     g.alpha = float(alpha)
     g.alpha_dev = lib.ptr(alpha_dev)
+    g.colsum_out, g.colsum_accumulate = lib.ptr(colsum_out), int(colsum_accumulate)
     lib.check(L.hs_gemm(ctypes.byref(g), lib.stream_ptr()), 'hs_gemm')
     return out
 
@@ -67,15 +69,16 @@ def ln_fwd(x, bias, residual, gamma, beta, *, eps=1e-12, p=0.0, seed=None, site=
 
 
 def ln_bwd(dy, z, gamma, mean, rstd, dgamma, dbeta, accumulate_params, *, p=0.0, seed=None, site=0,
-           post_dropout=False, need_dx=True):
-    """Returns (dz, dx). dgamma/dbeta are fp32 views (main grads) written or accumulated in place."""
+           post_dropout=False, need_dx=True, dbias=None, accumulate_bias=False):
+    """Returns (dz, dx). dgamma/dbeta are fp32 views (main grads) written or accumulated in place;
+    ``dbias`` (optional fp32 [H]) receives the column sums of dx."""
     L = lib.load()
     M, H = dy.shape
     dz = torch.empty_like(dy)
     dx = torch.empty_like(dy) if (need_dx and p > 0.0 and not post_dropout) else None
     lib.check(L.hs_ln_bwd(dy.data_ptr(), z.data_ptr(), gamma.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
                           dz.data_ptr(), lib.ptr(dx), lib.ptr(dgamma), lib.ptr(dbeta), int(accumulate_params),
-                          M, H, float(p), lib.ptr(seed), int(site), int(post_dropout),
+                          lib.ptr(dbias), int(accumulate_bias), M, H, float(p), lib.ptr(seed), int(site), int(post_dropout),
                           lib.dtype_code(dy.dtype), lib.stream_ptr()), 'hs_ln_bwd')
     return dz, (dx if dx is not None else dz)
 

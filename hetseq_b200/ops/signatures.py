@@ -9,7 +9,7 @@ SIGNATURES = {
     'hs_sumsq': [vp, ci, cl, ci, cl, vp, vp, ci, vp],
     'hs_adam_flat': [vp, vp, vp, vp, vp, ci, cl, ci, cl, cf, cf, cf, cf, cf, cf, cf, vp, vp, vp, vp],
     'hs_ln_fwd': [vp, vp, vp, vp, vp, vp, vp, vp, vp, ci, ci, cf, cf, vp, cu, ci, ci, vp],
-    'hs_ln_bwd': [vp, vp, vp, vp, vp, vp, vp, vp, vp, ci, ci, ci, cf, vp, cu, ci, ci, vp],
+    'hs_ln_bwd': [vp, vp, vp, vp, vp, vp, vp, vp, vp, ci, vp, ci, ci, ci, cf, vp, cu, ci, ci, vp],
     'hs_colsum': [vp, ci, ci, ci, vp, ci, ci, vp],
     'hs_xent': [vp, ci, vp, ci, ci, ci, vp, vp, ci, ci, ci, vp],
     'hs_gather_rows': [vp, vp, ci, vp, ci, ci, vp],
@@ -19,7 +19,7 @@ SIGNATURES = {
     'hs_sum_over_batch': [vp, ci, cl, vp, ci, ci, vp],
     'hs_colsum_rows_where': [vp, vp, ci, cl, ci, ci, vp, ci, vp, ci, vp],
     'hs_attention_fwd': [vp, vp, vp, vp, ci, ci, ci, ci, cf, vp, cu, ci, vp],
-    'hs_attention_bwd': [vp, vp, vp, vp, vp, vp, ci, ci, ci, ci, cf, vp, cu, ci, vp],
+    'hs_attention_bwd': [vp, vp, vp, vp, vp, vp, vp, ci, ci, ci, ci, ci, cf, vp, cu, ci, vp],
     'hs_ipc_alloc': [csz, ctypes.POINTER(vp), ctypes.c_char_p],
     'hs_ipc_open': [ctypes.c_char_p, ctypes.POINTER(vp)],
     'hs_ipc_close': [vp],

@@ -26,6 +26,7 @@ import torch
 
 ALIGN = 128    # elements; 256 B for 16-bit params, 512 B for fp32
 CHUNK = 2048   # elements; ownership granule of the sharded optimizer (8 KiB of fp32 gradient)
+SMALL_PARAM_NUMEL = 16384   # biases / LayerNorm vectors: zeroed eagerly at the start of an update
 
 
 def _round_up(x: int, m: int) -> int:
@@ -99,6 +100,8 @@ class FlatParamBuffer(object):
         #: (2 for BERT's tied decoder / word-embedding matrix); the callback fires on the last one
         self._expected_notifications: List[int] = [1] * len(self.params)
         self._notifications: List[int] = [0] * len(self.params)
+        self._is_small = [p.numel() <= SMALL_PARAM_NUMEL for p in self.params]
+        self._small_grads = [g for g, sm in zip(self.main_grads, self._is_small) if sm]
         self.zero_grad()
 
     # -- gradient plumbing ----------------------------------------------------------------------
@@ -153,20 +156,39 @@ class FlatParamBuffer(object):
             self._written[i] = True
         return self.main_grads[i]
 
-    def zero_grad(self, set_to_zero: bool = True) -> None:
+    def zero_grad(self, set_to_zero: Optional[bool] = None) -> None:
         """Start a new accumulation window.
 
-        With ``set_to_zero`` the whole flat gradient is cleared with one memset. Native ops do not
-        need that (their first write in a window overwrites), so the trainer passes ``False`` when
-        every parameter is produced by such an op.
+        With ``set_to_zero`` the whole flat gradient is cleared with one memset (1.3 GB for BERT-large:
+        0.2 ms of HBM time per update). That is only needed when autograd accumulates straight into the
+        views (same parameter and gradient dtype). With separate fp32 main gradients every producer -- the
+        native ops through ``grad_target`` and the fold hook -- OVERWRITES on its first write of a window,
+        so the default (``None``) skips the memset there; ``finalize_grads`` clears whatever no producer
+        touched. Padding between parameters is never written by anyone and stays zero from allocation.
         """
+        same = self.param_dtype == self.grad_dtype
+        if set_to_zero is None:
+            set_to_zero = same
         if set_to_zero:
             self.flat_grad.zero_()
-        same = self.param_dtype == self.grad_dtype
+        elif self._small_grads:
+            # small parameters (biases, LayerNorm) are produced by kernels that accumulate with atomics; one
+            # multi-tensor fill here is cheaper than a memset node in front of each of those kernels
+            torch._foreach_zero_(self._small_grads)
         for i, p in enumerate(self.params):
             # after a memset every view is a valid partial sum, so later writes must accumulate
-            self._written[i] = bool(set_to_zero)
+            self._written[i] = bool(set_to_zero) or self._is_small[i]
             p.grad = self.main_grads[i] if same else None
+
+    def finalize_grads(self) -> None:
+        """End of the accumulation window: parameters that received no gradient at all (unused in this
+        update) get zeros instead of the previous window's values, and are reported ready."""
+        for i, w in enumerate(self._written):
+            if not w:
+                self.main_grads[i].zero_()
+                self._written[i] = True
+                if self.ready_callback is not None:
+                    self.ready_callback(i)
 
     def mark_all_written(self) -> None:
         for i in range(len(self._written)):

@@ -40,7 +40,8 @@ enum hs_gemm_act {
   HS_ACT_NONE = 0,
   HS_ACT_GELU = 1,      /* x*0.5*(1+erf(x/1.41421))  (bert_modeling.py:104-116) */
   HS_ACT_TANH = 2,      /* pooler (bert_modeling.py:514-515) */
-  HS_ACT_DGELU_MUL = 3  /* out = acc * gelu'(aux_in): dgrad through the FFN activation */
+  HS_ACT_DGELU_MUL = 3, /* out = acc * gelu'(aux_in): dgrad through the FFN activation */
+  HS_ACT_ADD_AUX = 4    /* out = acc (+bias) + aux_in: dgrad that also collects the residual-path gradient */
 };
 
 typedef struct hs_gemm_args {
@@ -60,11 +61,14 @@ typedef struct hs_gemm_args {
   const void* bias; /* [N] in in_dtype, or NULL */
   int act;          /* hs_gemm_act */
   void* aux_out;    /* HS_ACT_GELU: pre-activation (acc+bias) stored here when non-NULL, layout of C */
-  const void* aux_in; /* HS_ACT_DGELU_MUL: pre-activation, in_dtype, row stride ldaux */
+  const void* aux_in; /* HS_ACT_DGELU_MUL: pre-activation; HS_ACT_ADD_AUX: addend. in_dtype, row stride ldaux */
   int ldaux;
   int accumulate;   /* 1: C += result (read-modify-write); used by wgrad into the flat grad buffer */
   float alpha;      /* scales the accumulator before bias/activation */
   const float* alpha_dev; /* optional device scalar multiplied into alpha (e.g. the upstream loss gradient) */
+  float* colsum_out;      /* optional fp32 [N]: column sums of C (after the epilogue) are added here -- when C is
+                           * the output gradient of a Linear this is its bias gradient, for free */
+  int colsum_accumulate;  /* 0: colsum_out is cleared first (on the stream); 1: += */
 } hs_gemm_args;
 
 /* Replaces F.linear/cuBLAS at bert_modeling.py:352-354,387-391,409-413,423-427,514-515,525-528,547
@@ -124,10 +128,14 @@ HS_API int hs_ln_fwd(const void* x, const void* bias, const void* residual, cons
                      void* y, void* z, float* mean, float* rstd, int M, int H, float eps, float dropout_p,
                      const long long* seed, unsigned site, int post_dropout, int dtype, hs_stream_t stream);
 /* dz = dLN/dz (residual path), dx = dz * dropout mask (GEMM path, may be NULL), dgamma/dbeta fp32
- * (= or += per accumulate_params): per-block partial sums in registers/shared memory, then one
- * atomicAdd per block and column straight into the destination (the flat main-grad buffer). */
+ * (= or += per accumulate_params); dbias (optional, fp32 [H], = or += per accumulate_bias) receives the
+ * column sums of dx, i.e. the bias gradient of the Linear that produced x -- no separate reduction pass.
+ * Persistent kernel, one CTA per SM: rows stream through per-warp shared-memory rings filled by bulk
+ * async copies; per-column partials live in registers, meet in shared memory, then one atomicAdd per
+ * block and column goes straight into the destination (the flat main-grad buffer). */
 HS_API int hs_ln_bwd(const void* dy, const void* z, const void* gamma, const float* mean, const float* rstd,
                      void* dz, void* dx, float* dgamma, float* dbeta, int accumulate_params,
+                     float* dbias, int accumulate_bias,
                      int M, int H, float dropout_p, const long long* seed, unsigned site, int post_dropout,
                      int dtype, hs_stream_t stream);
 /* out[n] (= or +=) sum_m x[m,n] for a 16-bit [M,N] matrix: the bias gradients of every Linear. */
@@ -170,10 +178,11 @@ HS_API int hs_attention_supported(int S, int head_dim);
 HS_API int hs_attention_fwd(const void* qkv, const float* mask, void* ctx, float* lse, int B, int S, int heads,
                             int H, float dropout_p, const long long* seed, unsigned site, int dtype,
                             hs_stream_t stream);
-/* dqkv [M, 3H] from dctx [M,H]; recomputes the probabilities and the dropout mask. */
+/* dqkv [M, 3H] from dctx [M,H]; recomputes the probabilities and the dropout mask. dbias (optional, fp32
+ * [3H], = or += per accumulate_bias) receives the column sums of dqkv: the q/k/v bias gradient. */
 HS_API int hs_attention_bwd(const void* qkv, const float* mask, const void* ctx, const void* dctx, const float* lse,
-                            void* dqkv, int B, int S, int heads, int H, float dropout_p, const long long* seed,
-                            unsigned site, int dtype, hs_stream_t stream);
+                            void* dqkv, float* dbias, int accumulate_bias, int B, int S, int heads, int H,
+                            float dropout_p, const long long* seed, unsigned site, int dtype, hs_stream_t stream);
 
 /* ---- fused data-parallel gradient path over NVLink peer memory (csrc/comm_sm100.cu) ------------------- */
 /* Replaces DDP's bucketed NCCL all-reduce (controller.py:78-86, N4) + multiply_grads + clip_grad_norm +

@@ -76,6 +76,39 @@ def test_native_loss_and_grads_match_torch(tmp_path, flag):
     assert top[0][1] < (0.15 if flag == '--bf16' else 0.10), top
 
 
+def test_fused_layer_node_matches_per_op_nodes(tmp_path):
+    """EncoderLayerFn (one autograd node per layer, fused bias gradients / residual adds) against the
+    one-node-per-op path, dropout ON: both recompute the same Philox masks, so they must agree closely."""
+    from hetseq_b200.ops import rng
+    ctl, task = _build(str(tmp_path), '--fp16', 'native', hidden_dropout_prob=0.1, attention_probs_dropout_prob=0.1)
+    model = ctl.get_model()
+    nb = model.native
+    dev = task.prepare_sample(_batch(), ctl.device)
+    model.train()
+    grads, losses = [], []
+    for fused in (True, False):
+        nb.fused_layer = fused
+        rng.set_step_seed(4321, 0)
+        ctl.zero_grad()
+        loss = model(*dev)
+        (loss * 1024.0).backward()
+        ctl.optimizer.buffer.finalize_grads()
+        losses.append(loss.item())
+        grads.append(ctl.optimizer.buffer.flat_grad.clone())
+    nb.fused_layer = True
+    assert abs(losses[0] - losses[1]) < 1e-3, losses
+    rel = ((grads[0] - grads[1]).norm() / grads[1].norm()).item()
+    assert rel < 5e-3, rel
+    for name, p in model.named_parameters():
+        buf, i = p._hs_flat
+        a = grads[0][buf.offsets[i]:buf.offsets[i] + p.numel()]
+        b = grads[1][buf.offsets[i]:buf.offsets[i] + p.numel()]
+        if 'key.bias' in name:
+            continue
+        e = ((a - b).norm() / (b.norm() + 1e-6)).item()
+        assert e < 2e-2, (name, e)
+
+
 def test_native_training_reduces_loss(tmp_path):
     ctl, task = _build(str(tmp_path), '--fp16', 'native', hidden_dropout_prob=0.1, attention_probs_dropout_prob=0.1)
     sample = _batch()

@@ -74,6 +74,62 @@ def test_gemm_dgelu_epilogue(nat, dt):
 
 
 @pytest.mark.parametrize('dt', DT)
+@pytest.mark.parametrize('shape', [(256, 512, 384), (200, 264, 136), (4096, 1024, 1024)])
+def test_gemm_add_aux_and_colsum_epilogues(nat, dt, shape):
+    """dgrad that also adds the residual-path gradient (ACT_ADD_AUX) and the bias gradient collected in the
+    epilogue (colsum_out), incl. ragged edges and the dGELU epilogue."""
+    M, N, K = shape
+    torch.manual_seed(21)
+    dy = (torch.randn(M, K, device='cuda') * 0.1).to(dt)
+    w = (torch.randn(K, N, device='cuda') * 0.05).to(dt)
+    add = torch.randn(M, N, device='cuda').to(dt)
+    out = torch.empty(M, N, dtype=dt, device='cuda')
+    cs = torch.full((N,), 2.0, device='cuda')
+    nat.gemm(dy, w, out, M, N, K, lda=K, ldb=N, ldc=N, b_mn=True, act=nat.ACT_ADD_AUX, aux_in=add, ldaux=N,
+             colsum_out=cs, colsum_accumulate=True)
+    ref = dy.float() @ w.float() + add.float()
+    torch.testing.assert_close(out.float(), ref, **tol(dt))
+    torch.testing.assert_close(cs, ref.sum(0) + 2.0, rtol=2e-2, atol=0.3)
+    pre = torch.randn(M, N, device='cuda').to(dt)
+    cs2 = torch.full((N,), 7.0, device='cuda')     # overwritten, not accumulated
+    nat.gemm(dy, w, out, M, N, K, lda=K, ldb=N, ldc=N, b_mn=True, act=nat.ACT_DGELU_MUL, aux_in=pre, ldaux=N,
+             colsum_out=cs2, colsum_accumulate=False)
+    pr = pre.float().requires_grad_(True)
+    gelu_ref(pr).backward(dy.float() @ w.float())
+    torch.testing.assert_close(out.float(), pr.grad, **tol(dt))
+    torch.testing.assert_close(cs2, pr.grad.sum(0), rtol=2e-2, atol=5e-2)
+
+
+@pytest.mark.parametrize('dt', DT)
+@pytest.mark.parametrize('M', [300, 4096])
+def test_layernorm_bwd_many_rows(nat, dt, M):
+    """More rows than ring slots x warps x CTAs: exercises the refill path of the persistent kernel."""
+    H = 1024
+    torch.manual_seed(33)
+    M = M * 5 if M == 4096 else M
+    x = torch.randn(M, H, device='cuda').to(dt)
+    res = torch.randn(M, H, device='cuda').to(dt)
+    gamma = (1 + 0.1 * torch.randn(H, device='cuda')).to(dt)
+    beta = (0.1 * torch.randn(H, device='cuda')).to(dt)
+    y, z, mean, rstd = nat.ln_fwd(x, None, res, gamma, beta, p=0.0)
+    zr = z.float().requires_grad_(True)
+    g32, b32 = gamma.float().requires_grad_(True), beta.float().requires_grad_(True)
+    u = zr.mean(-1, keepdim=True)
+    sd = (zr - u).pow(2).mean(-1, keepdim=True)
+    yr = g32 * ((zr - u) / torch.sqrt(sd + 1e-12)) + b32
+    dy = (torch.randn(M, H, device='cuda') * 0.1).to(dt)
+    yr.backward(dy.float())
+    dgamma, dbeta, dbias = (torch.zeros(H, device='cuda') for _ in range(3))
+    dz, dx = nat.ln_bwd(dy, z, gamma, mean, rstd, dgamma, dbeta, False, dbias=dbias)
+    t = dict(rtol=3e-2, atol=3e-2) if dt == torch.bfloat16 else dict(rtol=1e-2, atol=1e-2)
+    torch.testing.assert_close(dz.float(), zr.grad, **t)
+    scale = math.sqrt(M)
+    torch.testing.assert_close(dgamma, g32.grad, rtol=3e-2, atol=0.02 * scale)
+    torch.testing.assert_close(dbeta, b32.grad, rtol=3e-2, atol=0.02 * scale)
+    torch.testing.assert_close(dbias, zr.grad.sum(0), rtol=3e-2, atol=0.02 * scale)
+
+
+@pytest.mark.parametrize('dt', DT)
 @pytest.mark.parametrize('H', [256, 768, 1024])
 @pytest.mark.parametrize('p', [0.0, 0.1])
 def test_layernorm_fwd_bwd(nat, dt, H, p):
@@ -111,8 +167,12 @@ def test_layernorm_fwd_bwd(nat, dt, H, p):
     yr.backward(dy.float())
     dgamma = torch.zeros(H, device='cuda')
     dbeta = torch.full((H,), 0.5, device='cuda')
-    dz, dx = nat.ln_bwd(dy, z, gamma, mean, rstd, dgamma, dbeta, False, p=p, seed=seed, site=7)
+    dbias = torch.full((H,), 0.25, device='cuda')
+    dz, dx = nat.ln_bwd(dy, z, gamma, mean, rstd, dgamma, dbeta, False, p=p, seed=seed, site=7, dbias=dbias,
+                        accumulate_bias=True)
     t = dict(rtol=3e-2, atol=3e-2) if dt == torch.bfloat16 else dict(rtol=1e-2, atol=1e-2)
+    # the fused bias gradient is the column sum of dx (on top of what the destination already held)
+    torch.testing.assert_close(dbias, xr.grad.sum(0) + 0.25, rtol=2e-2, atol=5e-2 if dt == torch.float16 else 2e-1)
     torch.testing.assert_close(dz.float(), rr.grad, **t)
     torch.testing.assert_close(dx.float(), xr.grad, **t)
     pt = dict(rtol=2e-2, atol=5e-2) if dt == torch.float16 else dict(rtol=3e-2, atol=2e-1)
@@ -258,6 +318,21 @@ def test_attention_fwd_bwd(dt):
     for name, sl in (('dq', slice(0, H)), ('dk', slice(H, 2 * H)), ('dv', slice(2 * H, 3 * H))):
         e = ((qkv.grad.float()[:, sl] - ref_in.grad[:, sl]).norm() / ref_in.grad[:, sl].norm()).item()
         assert e < (0.03 if dt == torch.bfloat16 else 0.006), (name, e)
+    # the q/k/v bias gradient collected by the backward kernel = column sums of dqkv
+    from hetseq_b200.ops import lib
+    L = lib.load()
+    lse = torch.empty(B * heads * S, dtype=torch.float32, device='cuda')
+    o2 = torch.empty(B * S, H, dtype=dt, device='cuda')
+    q2 = qkv.detach()
+    lib.check(L.hs_attention_fwd(q2.data_ptr(), mask.data_ptr(), o2.data_ptr(), lse.data_ptr(), B, S, heads, H, 0.0, None,
+                                 1, lib.dtype_code(dt), lib.stream_ptr()), 'fwd')
+    dq2 = torch.empty_like(q2)
+    dbias = torch.full((3 * H,), 1.5, device='cuda')
+    lib.check(L.hs_attention_bwd(q2.data_ptr(), mask.data_ptr(), o2.data_ptr(), dout.data_ptr(), lse.data_ptr(),
+                                 dq2.data_ptr(), dbias.data_ptr(), 1, B, S, heads, H, 0.0, None, 1, lib.dtype_code(dt),
+                                 lib.stream_ptr()), 'bwd')
+    assert torch.equal(dq2, qkv.grad)
+    torch.testing.assert_close(dbias, ref_in.grad.sum(0) + 1.5, rtol=2e-2, atol=0.05 if dt == torch.float16 else 0.3)
 
 
 def test_attention_dropout_consistency():
