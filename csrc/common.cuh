@@ -330,6 +330,15 @@ __device__ __forceinline__ float gelu_grad_ref(float x) {
   return 0.5f * (1.0f + erf_poly(u)) + x * __expf(-u * u) * (0.5641895835477563f * kGeluInv);
 }
 
+// gelu(x) and gelu'(x) together (they share the erf): forward can store the derivative for backward
+__device__ __forceinline__ void gelu_and_grad(const float x_in, float& y, float& dy) {
+  const float x = x_in;     // y may alias the argument
+  const float u = x * kGeluInv;
+  const float cdf = 0.5f * (1.0f + erf_poly(u));
+  y = x * cdf;
+  dy = cdf + x * __expf(-u * u) * (0.5641895835477563f * kGeluInv);
+}
+
 // ----------------------------------------------------------------------------------------------
 // Philox4x32-10 counter RNG: dropout masks are recomputed in backward from (seed, stream, index)
 // ----------------------------------------------------------------------------------------------

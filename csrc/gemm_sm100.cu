@@ -122,7 +122,10 @@ __device__ __forceinline__ void store_row32(T* __restrict__ p, int n0, int N, bo
 }
 
 // ---- the kernel -------------------------------------------------------------------------------
-template <int BN, typename InT, typename OutT, int CG>
+// ACT >= 0: the activation is a compile-time constant (the kernel only carries that epilogue: the all-in-one
+// epilogue is ~8.6 K instructions and ncu showed 19 % of the epilogue warps' stalls as instruction fetch);
+// ACT < 0: read it from GemmParams at run time.
+template <int BN, typename InT, typename OutT, int CG, int ACT>
 __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
                                           const CUtensorMap& tmAux, const GemmParams& p) {
   using Cfg = GemmCfg<BN, CG>;
@@ -145,7 +148,9 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
   uint64_t* tempty_bar = tfull_bar + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
 
-  const int warp = threadIdx.x >> 5;
+  // broadcast from lane 0: tells the compiler the role branches below are warp-uniform, so loop state of the
+  // producer and MMA warps lives in uniform registers (no R2UR / waterfall code around every TMA and MMA)
+  const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
   const int num_tiles = p.tiles_m * p.tiles_n;
   const int num_work = num_tiles * p.split_k;
@@ -178,17 +183,22 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
 
   if (warp == 0) {
     // ===================== TMA producer =====================
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int work = worker; work < num_work; work += nworkers) {
-        const int tile = work % num_tiles, ks = work / num_tiles;
-        const int tm = tile % p.tiles_m, tn = tile / p.tiles_m;
-        const int kb0 = ks * p.kb_per_split, kb1 = min(p.num_kb, kb0 + p.kb_per_split);
-        const int m_row = tm * TILE_M + cta_rank * BM;          // this CTA's rows of A
-        const int n_row = tn * BN + cta_rank * (BN / CG);       // this CTA's rows of B
-        for (int kb = kb0; kb < kb1; ++kb) {
-          mbar_wait(&empty_bar[stage], phase ^ 1);
+    // The whole warp walks the loop (uniform control flow); one elected lane issues the copies.
+    // (Measured and rejected: a second cursor that prefetches boxes into L2 ten k-blocks ahead. The layer
+    // shapes did not move and 8192^3 dropped from 2050 to 1410 TFLOP/s -- the L2 request path is the limiter,
+    // not HBM latency.)
+    int stage = 0;
+    uint32_t phase = 0;
+    const bool a_mn = p.a_mn != 0, b_mn = p.b_mn != 0;
+    for (int work = worker; work < num_work; work += nworkers) {
+      const int tile = work % num_tiles, ks = work / num_tiles;
+      const int tm = tile % p.tiles_m, tn = tile / p.tiles_m;
+      const int kb0 = ks * p.kb_per_split, kb1 = min(p.num_kb, kb0 + p.kb_per_split);
+      const int m_row = tm * TILE_M + cta_rank * BM;          // this CTA's rows of A
+      const int n_row = tn * BN + cta_rank * (BN / CG);       // this CTA's rows of B
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        if (elect_one_sync()) {
           // the leader's barrier collects the bytes of both CTAs of the pair
           if (leader) mbar_expect_tx(&full_bar[stage], CG * (A_STAGE_BYTES + B_STAGE_BYTES));
           uint8_t* a_dst = sA + stage * A_STAGE_BYTES;
@@ -197,20 +207,21 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
             if constexpr (CG == 2) tma_load_2d_2cta(dst, tm_, &full_bar[stage], c0, c1);
             else tma_load_2d(dst, tm_, &full_bar[stage], c0, c1);
           };
-          if (!p.a_mn) {
+          if (!a_mn) {
             load(a_dst, &tmA, kb * BK, m_row);
           } else {
 #pragma unroll
             for (int j = 0; j < BM / 64; ++j) load(a_dst + j * (BK * 128), &tmA, m_row + j * 64, kb * BK);
           }
-          if (!p.b_mn) {
+          if (!b_mn) {
             load(b_dst, &tmB, kb * BK, n_row);
           } else {
 #pragma unroll
             for (int j = 0; j < BN / CG / 64; ++j) load(b_dst + j * (BK * 128), &tmB, n_row + j * 64, kb * BK);
           }
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
+        __syncwarp();
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
@@ -219,6 +230,9 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
     uint32_t phase = 0;
     int as = 0;
     uint32_t aphase = 0;
+    const uint64_t adesc0 = umma_desc_sw128(smem_u32(sA), p.a_lbo, p.a_sbo);
+    const uint64_t bdesc0 = umma_desc_sw128(smem_u32(sB), p.b_lbo, p.b_sbo);
+    const uint32_t a_kadv16 = p.a_kadv >> 4, b_kadv16 = p.b_kadv >> 4;
     if (leader)
     for (int work = worker; work < num_work; work += nworkers) {
       const int ks = work / num_tiles;
@@ -230,18 +244,17 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
         mbar_wait(&full_bar[stage], phase);
         tc_fence_after();
         if (elect_one_sync()) {
-          const uint32_t a_addr = smem_u32(sA + stage * A_STAGE_BYTES);
-          const uint32_t b_addr = smem_u32(sB + stage * B_STAGE_BYTES);
-          const uint64_t adesc = umma_desc_sw128(a_addr, p.a_lbo, p.a_sbo);
-          const uint64_t bdesc = umma_desc_sw128(b_addr, p.b_lbo, p.b_sbo);
+          // descriptors differ from the stage-0 ones only in the 14-bit start-address field (bytes >> 4)
+          const uint64_t adesc = adesc0 + static_cast<uint64_t>(stage * (A_STAGE_BYTES >> 4));
+          const uint64_t bdesc = bdesc0 + static_cast<uint64_t>(stage * (B_STAGE_BYTES >> 4));
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
             if constexpr (CG == 2)
-              umma_f16_2cta(d_tmem, adesc + ((k * p.a_kadv) >> 4), bdesc + ((k * p.b_kadv) >> 4), p.idesc,
-                            (kb != kb0 || k != 0) ? 1u : 0u);
+              umma_f16_2cta(d_tmem, adesc + static_cast<uint64_t>(k * a_kadv16), bdesc + static_cast<uint64_t>(k * b_kadv16),
+                            p.idesc, (kb != kb0 || k != 0) ? 1u : 0u);
             else
-              umma_f16(d_tmem, adesc + ((k * p.a_kadv) >> 4), bdesc + ((k * p.b_kadv) >> 4), p.idesc,
-                       (kb != kb0 || k != 0) ? 1u : 0u);
+              umma_f16(d_tmem, adesc + static_cast<uint64_t>(k * a_kadv16), bdesc + static_cast<uint64_t>(k * b_kadv16),
+                       p.idesc, (kb != kb0 || k != 0) ? 1u : 0u);
           }
           if constexpr (CG == 2) {
             umma_commit_2cta(&empty_bar[stage], 3);                  // frees the slot in both CTAs
@@ -266,7 +279,27 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
     const bool tma = p.tma_store != 0;
     const float alpha = p.alpha * (p.alpha_dev != nullptr ? *p.alpha_dev : 1.0f);
     constexpr int CW = (sizeof(OutT) == 2) ? 64 : 32;   // columns per 128-byte staging row
+    constexpr int NCH = (BN / 2) / CW;                  // chunks per tile for this warp
+    const int act = ACT >= 0 ? ACT : p.act;
+    const bool use_aux = act == HS_ACT_DGELU_MUL || act == HS_ACT_ADD_AUX || act == HS_ACT_MUL_AUX;
     uint8_t* stg = sStage + (warp - 2) * 4096;
+    // The epilogue operand (pre-activation for dGELU, residual-path gradient for ADD) is this thread's own row:
+    // CW 16-bit values = CW/8 16-byte loads. ncu showed the warps stalled on the long scoreboard right after
+    // these loads, so they are issued early: an L2 prefetch of the warp's whole part of the tile and the loads
+    // of the first chunk go out BEFORE the wait for the accumulator (the main loop hides HBM latency), the
+    // loads of the next chunk right after the current chunk's values have been consumed (the output staging
+    // and the next TMEM read hide L2 latency). One register buffer, so no extra pressure.
+    uint4 ax[CW / 8];
+    bool ax_ok = false;
+    auto aux_issue = [&](int m_, int n0_) {
+      ax_ok = use_aux && vec && m_ < p.M && n0_ + CW <= p.N;
+      if (ax_ok) {
+        const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const InT*>(p.aux_in) +
+                                                          static_cast<size_t>(m_) * p.ldaux + n0_);
+#pragma unroll
+        for (int j = 0; j < CW / 8; ++j) ax[j] = __ldg(src + j);
+      }
+    };
     int as = 0;
     uint32_t aphase = 0;
     for (int work = worker; work < num_work; work += nworkers) {
@@ -276,24 +309,22 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
       const int m0 = tm * TILE_M + cta_rank * BM + q * 32;
       const int m = m0 + lane;
       const bool row_ok = m < p.M;
-      // The epilogue operand (pre-activation for dGELU, residual-path gradient for ADD) is read row by row
-      // with per-thread loads; start pulling this warp's part of the tile towards L2 now, while the main loop
-      // of this tile is still running, so that those loads do not pay HBM latency later.
-      if (p.aux_in != nullptr && row_ok) {
+      if (use_aux && row_ok) {
         const InT* arow = reinterpret_cast<const InT*>(p.aux_in) + static_cast<size_t>(m) * p.ldaux;
 #pragma unroll
-        for (int cc = 0; cc < (BN / 2) / CW; ++cc) {
+        for (int cc = 1; cc < NCH; ++cc) {
           const int n0 = n_base + half * (BN / 2) + cc * CW;
           if (n0 < p.N) asm volatile("prefetch.global.L2 [%0];" ::"l"(arow + n0));
         }
       }
+      aux_issue(m, n_base + half * (BN / 2));
       mbar_wait(&tfull_bar[as], aphase);
       __syncwarp();
       tc_fence_after();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
       const bool add_bias = bias != nullptr && ks == 0;
 #pragma unroll 1
-      for (int cc = 0; cc < (BN / 2) / CW; ++cc) {
+      for (int cc = 0; cc < NCH; ++cc) {
         const int c0 = half * (BN / 2) + cc * CW;
         const int n0 = n_base + c0;
         if (n0 >= p.N) break;  // warp-uniform
@@ -323,7 +354,16 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
           }
         }
         // ---- activation (pre-activation goes out first when requested)
-        if (p.act == HS_ACT_GELU) {
+        if (act == HS_ACT_GELU || act == HS_ACT_GELU_DAUX) {
+          const bool daux = act == HS_ACT_GELU_DAUX;
+          float av[CW];     // what goes to aux_out: the pre-activation, or the derivative of the activation
+          if (daux) {
+#pragma unroll
+            for (int i = 0; i < CW; ++i) gelu_and_grad(v[i], v[i], av[i]);
+          } else {
+#pragma unroll
+            for (int i = 0; i < CW; ++i) av[i] = v[i];
+          }
           if (p.aux_out != nullptr) {
             if constexpr (sizeof(OutT) == 2) {
               if (tma) {
@@ -332,8 +372,8 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
                   uint4 u;
-                  u.x = Cvt<InT>::pack2(v[j * 8 + 0], v[j * 8 + 1]); u.y = Cvt<InT>::pack2(v[j * 8 + 2], v[j * 8 + 3]);
-                  u.z = Cvt<InT>::pack2(v[j * 8 + 4], v[j * 8 + 5]); u.w = Cvt<InT>::pack2(v[j * 8 + 6], v[j * 8 + 7]);
+                  u.x = Cvt<InT>::pack2(av[j * 8 + 0], av[j * 8 + 1]); u.y = Cvt<InT>::pack2(av[j * 8 + 2], av[j * 8 + 3]);
+                  u.z = Cvt<InT>::pack2(av[j * 8 + 4], av[j * 8 + 5]); u.w = Cvt<InT>::pack2(av[j * 8 + 6], av[j * 8 + 7]);
                   *reinterpret_cast<uint4*>(stg + lane * 128 + ((j ^ (lane & 7)) << 4)) = u;
                 }
                 fence_proxy_async_smem();
@@ -348,37 +388,47 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
                 for (int sub = 0; sub < CW / 32; ++sub) {
                   float t32[32];
 #pragma unroll
-                  for (int i = 0; i < 32; ++i) t32[i] = v[sub * 32 + i];
+                  for (int i = 0; i < 32; ++i) t32[i] = av[sub * 32 + i];
                   store_row32<InT>(reinterpret_cast<InT*>(p.aux_out) + static_cast<size_t>(m) * p.ldaux, n0 + sub * 32, p.N, vec, t32);
                 }
               }
             }
           }
+          if (act == HS_ACT_GELU) {
 #pragma unroll
-          for (int i = 0; i < CW; ++i) v[i] = gelu_ref(v[i]);
-        } else if (p.act == HS_ACT_TANH) {
+            for (int i = 0; i < CW; ++i) v[i] = gelu_ref(v[i]);
+          }
+        } else if (act == HS_ACT_TANH) {
 #pragma unroll
           for (int i = 0; i < CW; ++i) v[i] = tanhf(v[i]);
-        } else if (p.act == HS_ACT_DGELU_MUL) {
-          if (row_ok) {
+        } else if (use_aux) {
+          if (ax_ok) {
+#pragma unroll
+            for (int j = 0; j < CW / 8; ++j) {
+              const float2 f0 = Cvt<InT>::unpack2(ax[j].x), f1 = Cvt<InT>::unpack2(ax[j].y),
+                           f2 = Cvt<InT>::unpack2(ax[j].z), f3 = Cvt<InT>::unpack2(ax[j].w);
+              const float x[8] = {f0.x, f0.y, f1.x, f1.y, f2.x, f2.y, f3.x, f3.y};
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                if (act == HS_ACT_DGELU_MUL) v[j * 8 + i] *= gelu_grad_ref(x[i]);
+                else if (act == HS_ACT_MUL_AUX) v[j * 8 + i] *= x[i];
+                else v[j * 8 + i] += x[i];
+              }
+            }
+          } else if (row_ok) {   // ragged edge / unaligned operand: synchronous element-wise loads
 #pragma unroll
             for (int sub = 0; sub < CW / 32; ++sub) {
               float x[32];
-              load_row32<InT>(reinterpret_cast<const InT*>(p.aux_in) + static_cast<size_t>(m) * p.ldaux, n0 + sub * 32, p.N, vec, x);
+              load_row32<InT>(reinterpret_cast<const InT*>(p.aux_in) + static_cast<size_t>(m) * p.ldaux, n0 + sub * 32, p.N, false, x);
 #pragma unroll
-              for (int i = 0; i < 32; ++i) v[sub * 32 + i] *= gelu_grad_ref(x[i]);
+              for (int i = 0; i < 32; ++i) {
+                if (act == HS_ACT_DGELU_MUL) v[sub * 32 + i] *= gelu_grad_ref(x[i]);
+                else if (act == HS_ACT_MUL_AUX) v[sub * 32 + i] *= x[i];
+                else v[sub * 32 + i] += x[i];
+              }
             }
           }
-        } else if (p.act == HS_ACT_ADD_AUX) {
-          if (row_ok) {
-#pragma unroll
-            for (int sub = 0; sub < CW / 32; ++sub) {
-              float x[32];
-              load_row32<InT>(reinterpret_cast<const InT*>(p.aux_in) + static_cast<size_t>(m) * p.ldaux, n0 + sub * 32, p.N, vec, x);
-#pragma unroll
-              for (int i = 0; i < 32; ++i) v[sub * 32 + i] += x[i];
-            }
-          }
+          if (cc + 1 < NCH) aux_issue(m, n0 + CW);
         }
         // ---- output
         if (tma) {
@@ -468,16 +518,17 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmAux,
                     const GemmParams p) {
-  gemm_body<BN, InT, OutT, 1>(tmA, tmB, tmC, tmAux, p);
+  gemm_body<BN, InT, OutT, 1, -1>(tmA, tmB, tmC, tmAux, p);
 }
 
-// CTA-pair variant: tcgen05.mma.cta_group::2 with UMMA_M = 256 (the pair's 256 x 256 tile)
-template <typename InT, typename OutT>
+// CTA-pair variant: tcgen05.mma.cta_group::2 with UMMA_M = 256 (the pair's 256 x 256 tile); one instance per
+// epilogue kind (ACT = -1: generic)
+template <typename InT, typename OutT, int ACT>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
 gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                          const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmAux,
                          const GemmParams p) {
-  gemm_body<256, InT, OutT, 2>(tmA, tmB, tmC, tmAux, p);
+  gemm_body<256, InT, OutT, 2, ACT>(tmA, tmB, tmC, tmAux, p);
 }
 
 // ---- host side --------------------------------------------------------------------------------
@@ -544,14 +595,26 @@ static int launch_gemm(const hs_gemm_args& a, cudaStream_t stream) {
   using Cfg = GemmCfg<BN, CG>;
   constexpr int TILE_M = BM * CG;
   void (*kern)(CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, GemmParams);
-  if constexpr (CG == 2) kern = gemm_tcgen05_2cta_kernel<InT, OutT>;
-  else kern = gemm_tcgen05_kernel<BN, InT, OutT>;
-  static bool attr_done[64] = {false};
+  int variant = 0;
+  if constexpr (CG == 2) {
+    kern = gemm_tcgen05_2cta_kernel<InT, OutT, -1>;
+    if (a.act == HS_ACT_NONE) { kern = gemm_tcgen05_2cta_kernel<InT, OutT, HS_ACT_NONE>; variant = 1; }
+    if constexpr (sizeof(OutT) == 2) {
+      if (a.act == HS_ACT_GELU) { kern = gemm_tcgen05_2cta_kernel<InT, OutT, HS_ACT_GELU>; variant = 2; }
+      else if (a.act == HS_ACT_DGELU_MUL) { kern = gemm_tcgen05_2cta_kernel<InT, OutT, HS_ACT_DGELU_MUL>; variant = 3; }
+      else if (a.act == HS_ACT_ADD_AUX) { kern = gemm_tcgen05_2cta_kernel<InT, OutT, HS_ACT_ADD_AUX>; variant = 4; }
+      else if (a.act == HS_ACT_GELU_DAUX) { kern = gemm_tcgen05_2cta_kernel<InT, OutT, HS_ACT_GELU_DAUX>; variant = 5; }
+      else if (a.act == HS_ACT_MUL_AUX) { kern = gemm_tcgen05_2cta_kernel<InT, OutT, HS_ACT_MUL_AUX>; variant = 6; }
+    }
+  } else {
+    kern = gemm_tcgen05_kernel<BN, InT, OutT>;
+  }
+  static bool attr_done[64][7] = {};
   int dev = 0;
   HS_CUDA_OK(cudaGetDevice(&dev));
-  if (dev < 64 && !attr_done[dev]) {
+  if (dev < 64 && !attr_done[dev][variant]) {
     HS_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
-    attr_done[dev] = true;
+    attr_done[dev][variant] = true;
   }
   CUtensorMap tmA, tmB;
   int rc;
@@ -647,7 +710,14 @@ extern "C" int hs_gemm(const hs_gemm_args* args, hs_stream_t stream) {
     set_last_error("hs_gemm: A and B must be 16-byte aligned");
     return 1;
   }
-  if ((a.act == HS_ACT_DGELU_MUL || a.act == HS_ACT_ADD_AUX) && a.aux_in == nullptr) { set_last_error("hs_gemm: DGELU_MUL / ADD_AUX need aux_in"); return 1; }
+  if ((a.act == HS_ACT_DGELU_MUL || a.act == HS_ACT_ADD_AUX || a.act == HS_ACT_MUL_AUX) && a.aux_in == nullptr) {
+    set_last_error("hs_gemm: DGELU_MUL / ADD_AUX / MUL_AUX need aux_in");
+    return 1;
+  }
+  if (a.act == HS_ACT_GELU_DAUX && (a.aux_out == nullptr || a.out_dtype == HS_F32)) {
+    set_last_error("hs_gemm: GELU_DAUX needs aux_out and a 16-bit output");
+    return 1;
+  }
   // Tile-width heuristic: prefer 128x256 tiles (fewer B re-reads) unless 128x128 fills the SMs better.
   const int sms = num_sms();
   const long tm = (a.M + BM - 1) / BM;

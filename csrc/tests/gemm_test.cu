@@ -149,7 +149,8 @@ static int run_case(const Case& c) {
   return ok ? 0 : 1;
 }
 
-static void perf(const char* name, int M, int N, int K, int a_mn, int b_mn, int out_f32, int act, int bias) {
+static void perf(const char* name, int M, int N, int K, int a_mn, int b_mn, int out_f32, int act, int bias,
+                 int colsum = 0) {
   auto r8 = [](int x) { return (x + 7) / 8 * 8; };
   const int lda = a_mn ? r8(M) : r8(K), ldb = b_mn ? r8(N) : r8(K), ldc = r8(N);
   const size_t a_rows = a_mn ? K : M, b_rows = b_mn ? K : N;
@@ -164,7 +165,10 @@ static void perf(const char* name, int M, int N, int K, int a_mn, int b_mn, int 
   g.A = dA; g.B = dB; g.C = dC; g.M = M; g.N = N; g.K = K; g.lda = lda; g.ldb = ldb; g.ldc = ldc;
   g.a_mn_major = a_mn; g.b_mn_major = b_mn; g.in_dtype = HS_BF16; g.out_dtype = out_f32 ? HS_F32 : HS_BF16;
   g.bias = bias ? dbias : nullptr; g.act = act; g.aux_out = act == HS_ACT_GELU ? daux : nullptr;
-  g.aux_in = act == HS_ACT_DGELU_MUL ? daux : nullptr; g.ldaux = ldc; g.alpha = 1.0f;
+  g.aux_in = (act == HS_ACT_DGELU_MUL || act == HS_ACT_ADD_AUX || act == HS_ACT_MUL_AUX) ? daux : nullptr; g.ldaux = ldc; g.alpha = 1.0f;
+  if (act == HS_ACT_GELU_DAUX) g.aux_out = daux;
+  void* dcs = nullptr;
+  if (colsum) { CK(cudaMalloc(&dcs, N * 4)); CK(cudaMemset(dcs, 0, N * 4)); g.colsum_out = (float*)dcs; g.colsum_accumulate = 1; }
   cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
   for (int i = 0; i < 3; ++i) if (hs_gemm(&g, nullptr)) { printf("perf %s: %s\n", name, hs_last_error()); return; }
   CK(cudaDeviceSynchronize());
@@ -191,6 +195,8 @@ int main(int argc, char** argv) {
     if (!strcmp(w, "qkv")) perf("qkv fwd", 4096, 3072, 1024, 0, 0, 0, 0, 1);
     else if (!strcmp(w, "ffn1")) perf("ffn1 fwd gelu", 4096, 4096, 1024, 0, 0, 0, HS_ACT_GELU, 1);
     else if (!strcmp(w, "wgrad")) perf("ffn1 wgrad f32", 4096, 1024, 4096, 1, 1, 1, 0, 0);
+    else if (!strcmp(w, "ffn2")) perf("ffn2 fwd", 4096, 1024, 4096, 0, 0, 0, 0, 1);
+    else if (!strcmp(w, "dgelu")) perf("ffn2 dgrad dgelu + colsum", 4096, 4096, 1024, 0, 1, 0, HS_ACT_DGELU_MUL, 0, 1);
     else perf("square 8192", 8192, 8192, 8192, 0, 0, 0, 0, 0);
     return 0;
   }
@@ -224,6 +230,13 @@ int main(int argc, char** argv) {
     perf("ffn2 fwd", 4096, 1024, 4096, 0, 0, 0, 0, 1);
     perf("ffn1 dgrad", 4096, 1024, 4096, 0, 1, 0, 0, 0);
     perf("ffn2 dgrad dgelu", 4096, 4096, 1024, 0, 1, 0, HS_ACT_DGELU_MUL, 0);
+    perf("ffn2 dgrad dgelu + colsum", 4096, 4096, 1024, 0, 1, 0, HS_ACT_DGELU_MUL, 0, 1);
+    perf("ffn2 dgrad plain", 4096, 4096, 1024, 0, 1, 0, 0, 0);
+    perf("ffn1 fwd gelu + derivative", 4096, 4096, 1024, 0, 0, 0, HS_ACT_GELU_DAUX, 1);
+    perf("ffn2 dgrad x aux + colsum", 4096, 4096, 1024, 0, 1, 0, HS_ACT_MUL_AUX, 0, 1);
+    perf("ffn1 dgrad + add", 4096, 1024, 4096, 0, 1, 0, HS_ACT_ADD_AUX, 0);
+    perf("qkv dgrad + add", 4096, 1024, 3072, 0, 1, 0, HS_ACT_ADD_AUX, 0);
+    perf("qkv wgrad f32", 3072, 1024, 4096, 1, 1, 1, 0, 0);
     perf("ffn1 wgrad f32", 4096, 1024, 4096, 1, 1, 1, 0, 0);
     perf("ffn2 wgrad f32", 1024, 4096, 4096, 1, 1, 1, 0, 0);
     perf("attn-out wgrad f32", 1024, 1024, 4096, 1, 1, 1, 0, 0);

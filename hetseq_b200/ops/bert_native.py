@@ -28,7 +28,8 @@ import torch
 import torch.nn.functional as F
 
 from hetseq_b200.ops import lib, native, rng
-from hetseq_b200.ops.native import ACT_ADD_AUX, ACT_DGELU_MUL, ACT_GELU, ACT_NONE, ACT_TANH
+from hetseq_b200.ops.native import (ACT_ADD_AUX, ACT_DGELU_MUL, ACT_GELU, ACT_GELU_DAUX, ACT_MUL_AUX, ACT_NONE,
+                                    ACT_TANH)
 
 
 def _flat(p):
@@ -227,21 +228,23 @@ class EncoderLayerFn(torch.autograd.Function):
         x1, z1, mean1, rstd1 = native.ln_fwd(ao, None, x, so.LayerNorm.weight, so.LayerNorm.bias, eps=1e-12, p=p_h,
                                              seed=seed, site=s_ao)
         del ao
-        pre = torch.empty(M, I, dtype=dt, device=dev)
+        # FFN1: the epilogue emits gelu(pre) AND gelu'(pre) (they share the erf); backward then only multiplies
+        dact = torch.empty(M, I, dtype=dt, device=dev)
         h = torch.empty(M, I, dtype=dt, device=dev)
-        native.gemm(x1, inter.weight, h, M, I, H, lda=H, ldb=H, ldc=I, bias=inter.bias, act=ACT_GELU, aux_out=pre, ldaux=I)
+        native.gemm(x1, inter.weight, h, M, I, H, lda=H, ldb=H, ldc=I, bias=inter.bias, act=ACT_GELU_DAUX, aux_out=dact,
+                    ldaux=I)
         f = torch.empty(M, H, dtype=dt, device=dev)
         native.gemm(h, out.dense.weight, f, M, H, I, lda=I, ldb=I, ldc=H, bias=out.dense.bias)
         x2, z2, mean2, rstd2 = native.ln_fwd(f, None, x1, out.LayerNorm.weight, out.LayerNorm.bias, eps=1e-12, p=p_h,
                                              seed=seed, site=s_ffn)
         del f
-        ctx.save_for_backward(x, add_mask, qkv, ctxv, lse, z1, mean1, rstd1, x1, pre, h, z2, mean2, rstd2)
+        ctx.save_for_backward(x, add_mask, qkv, ctxv, lse, z1, mean1, rstd1, x1, dact, h, z2, mean2, rstd2)
         ctx.meta = (nb, layer, p_attn, p_h, B, S)
         return x2
 
     @staticmethod
     def backward(ctx, dx2):
-        x, add_mask, qkv, ctxv, lse, z1, mean1, rstd1, x1, pre, h, z2, mean2, rstd2 = ctx.saved_tensors
+        x, add_mask, qkv, ctxv, lse, z1, mean1, rstd1, x1, dact, h, z2, mean2, rstd2 = ctx.saved_tensors
         nb, layer, p_attn, p_h, B, S = ctx.meta
         L = lib.load()
         H, I, heads = nb.H, nb.I, nb.heads
@@ -263,7 +266,7 @@ class EncoderLayerFn(torch.autograd.Function):
         # ---- FFN
         b1g, b1acc = _wgrad_target([inter.bias])
         dpre = torch.empty(M, I, dtype=dt, device=dev)
-        native.gemm(df, out.dense.weight, dpre, M, I, H, lda=H, ldb=I, ldc=I, b_mn=True, act=ACT_DGELU_MUL, aux_in=pre,
+        native.gemm(df, out.dense.weight, dpre, M, I, H, lda=H, ldb=I, ldc=I, b_mn=True, act=ACT_MUL_AUX, aux_in=dact,
                     ldaux=I, colsum_out=b1g, colsum_accumulate=b1acc)
         wg2, acc2 = _wgrad_target([out.dense.weight])
         native.gemm(df, h, wg2, H, I, M, lda=H, ldb=I, ldc=I, a_mn=True, b_mn=True, accumulate=acc2)

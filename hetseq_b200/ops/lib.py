@@ -15,7 +15,7 @@ import torch
 _lib: Optional[ctypes.CDLL] = None
 
 HS_F16, HS_BF16, HS_F32 = 0, 1, 2
-ACT_NONE, ACT_GELU, ACT_TANH, ACT_DGELU_MUL, ACT_ADD_AUX = 0, 1, 2, 3, 4
+ACT_NONE, ACT_GELU, ACT_TANH, ACT_DGELU_MUL, ACT_ADD_AUX, ACT_GELU_DAUX, ACT_MUL_AUX = 0, 1, 2, 3, 4, 5, 6
 
 _DT = {torch.float16: HS_F16, torch.bfloat16: HS_BF16, torch.float32: HS_F32}
 

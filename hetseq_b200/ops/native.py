@@ -11,7 +11,8 @@ from typing import Optional
 import torch
 
 from hetseq_b200.ops import lib
-from hetseq_b200.ops.lib import ACT_ADD_AUX, ACT_DGELU_MUL, ACT_GELU, ACT_NONE, ACT_TANH  # noqa: F401
+from hetseq_b200.ops.lib import (ACT_ADD_AUX, ACT_DGELU_MUL, ACT_GELU, ACT_GELU_DAUX, ACT_MUL_AUX,  # noqa: F401
+                                 ACT_NONE, ACT_TANH)
 
 _scratch = {}
 

@@ -41,7 +41,10 @@ enum hs_gemm_act {
   HS_ACT_GELU = 1,      /* x*0.5*(1+erf(x/1.41421))  (bert_modeling.py:104-116) */
   HS_ACT_TANH = 2,      /* pooler (bert_modeling.py:514-515) */
   HS_ACT_DGELU_MUL = 3, /* out = acc * gelu'(aux_in): dgrad through the FFN activation */
-  HS_ACT_ADD_AUX = 4    /* out = acc (+bias) + aux_in: dgrad that also collects the residual-path gradient */
+  HS_ACT_ADD_AUX = 4,   /* out = acc (+bias) + aux_in: dgrad that also collects the residual-path gradient */
+  HS_ACT_GELU_DAUX = 5, /* like HS_ACT_GELU, but aux_out receives gelu'(pre-activation) instead of the
+                         * pre-activation: backward then only multiplies (HS_ACT_MUL_AUX) */
+  HS_ACT_MUL_AUX = 6    /* out = acc * aux_in */
 };
 
 typedef struct hs_gemm_args {
@@ -60,8 +63,10 @@ typedef struct hs_gemm_args {
   int out_dtype; /* HS_F16 | HS_BF16 | HS_F32 (C); 16-bit output must equal in_dtype */
   const void* bias; /* [N] in in_dtype, or NULL */
   int act;          /* hs_gemm_act */
-  void* aux_out;    /* HS_ACT_GELU: pre-activation (acc+bias) stored here when non-NULL, layout of C */
-  const void* aux_in; /* HS_ACT_DGELU_MUL: pre-activation; HS_ACT_ADD_AUX: addend. in_dtype, row stride ldaux */
+  void* aux_out;    /* HS_ACT_GELU: pre-activation (acc+bias), HS_ACT_GELU_DAUX: gelu'(acc+bias); stored when
+                     * non-NULL, layout of C */
+  const void* aux_in; /* HS_ACT_DGELU_MUL: pre-activation; HS_ACT_ADD_AUX: addend; HS_ACT_MUL_AUX: factor.
+                       * in_dtype, row stride ldaux */
   int ldaux;
   int accumulate;   /* 1: C += result (read-modify-write); used by wgrad into the flat grad buffer */
   float alpha;      /* scales the accumulator before bias/activation */

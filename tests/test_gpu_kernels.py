@@ -101,6 +101,32 @@ def test_gemm_add_aux_and_colsum_epilogues(nat, dt, shape):
 
 
 @pytest.mark.parametrize('dt', DT)
+@pytest.mark.parametrize('shape', [(256, 512, 384), (200, 264, 136), (4096, 4096, 1024)])
+def test_gemm_gelu_with_derivative_then_mul(nat, dt, shape):
+    """Forward epilogue that stores gelu'(pre) (ACT_GELU_DAUX) and the backward epilogue that multiplies by it
+    (ACT_MUL_AUX): together they must reproduce autograd through the erf GELU."""
+    M, N, K = shape
+    torch.manual_seed(22)
+    x = (torch.randn(M, K, device='cuda') * 0.5).to(dt)
+    w = (torch.randn(N, K, device='cuda') * 0.05).to(dt)
+    b = torch.randn(N, device='cuda').to(dt)
+    y = torch.empty(M, N, dtype=dt, device='cuda')
+    dact = torch.empty(M, N, dtype=dt, device='cuda')
+    nat.gemm(x, w, y, M, N, K, lda=K, ldb=K, ldc=N, bias=b, act=nat.ACT_GELU_DAUX, aux_out=dact, ldaux=N)
+    pre = (x.float() @ w.float().t() + b.float()).requires_grad_(True)
+    ref = gelu_ref(pre)
+    torch.testing.assert_close(y.float(), ref, **tol(dt))
+    ref.sum().backward()
+    torch.testing.assert_close(dact.float(), pre.grad, **tol(dt))
+    K2 = 256
+    dy = (torch.randn(M, K2, device='cuda') * 0.1).to(dt)
+    w2 = (torch.randn(K2, N, device='cuda') * 0.05).to(dt)
+    out = torch.empty(M, N, dtype=dt, device='cuda')
+    nat.gemm(dy, w2, out, M, N, K2, lda=K2, ldb=N, ldc=N, b_mn=True, act=nat.ACT_MUL_AUX, aux_in=dact, ldaux=N)
+    torch.testing.assert_close(out.float(), (dy.float() @ w2.float()) * dact.float(), **tol(dt))
+
+
+@pytest.mark.parametrize('dt', DT)
 @pytest.mark.parametrize('M', [300, 4096])
 def test_layernorm_bwd_many_rows(nat, dt, M):
     """More rows than ring slots x warps x CTAs: exercises the refill path of the persistent kernel."""
