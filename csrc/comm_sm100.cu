@@ -63,6 +63,36 @@ __device__ __forceinline__ float4 ld_relaxed_sys_f4(const float4* p) {
                : "memory");
   return v;
 }
+// Streaming variants for the reduce-scatter: 1.3 GB of gradients pass through once. Without a hint they are
+// allocated in L2 with normal priority -- on the reading GPU for its own copy and on the serving GPU for peer
+// reads -- and evict the activation / weight tiles that backward's GEMMs re-read from L2 (measured on 2 GPUs:
+// backward 1.0 ms slower while the reduce kernels ran next to it). evict_first keeps them out of the way.
+__device__ __forceinline__ uint64_t l2_evict_first_policy() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ float4 ld_peer_stream_f4(const float4* p, uint64_t pol) {
+  float4 v;
+  asm volatile("ld.relaxed.sys.global.L1::no_allocate.L2::cache_hint.v4.f32 {%0, %1, %2, %3}, [%4], %5;"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p), "l"(pol)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 ld_local_stream_f4(const float4* p, uint64_t pol) {
+  float4 v;
+  asm volatile("ld.global.L1::no_allocate.L2::cache_hint.v4.f32 {%0, %1, %2, %3}, [%4], %5;"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p), "l"(pol)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_local_stream_f4(float4* p, float4 v, uint64_t pol) {
+  asm volatile("st.global.L2::cache_hint.v4.f32 [%0], {%1, %2, %3, %4}, %5;"
+               ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "l"(pol)
+               : "memory");
+}
 __device__ __forceinline__ void st_relaxed_sys_u2(uint2* p, uint2 v) {
   asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(v.x), "r"(v.y) : "memory");
 }
@@ -104,28 +134,30 @@ dp_reduce_scatter_kernel(PeerTable grads, PeerTable sigs, int rank, int W, long 
   const int vec_per_chunk = chunk / 4;
   float acc = 0.f;
   float* mine = reinterpret_cast<float*>(grads.ptr[rank]);
+  const uint64_t pol = l2_evict_first_policy();
   for (long long c = first + static_cast<long long>(blockIdx.x) * W; c < chunk_end; c += static_cast<long long>(gridDim.x) * W) {
     const long long base = c * chunk;
     // two vectors per thread and all peers' loads issued before the first add: (W-1)*2 NVLink loads in flight
     for (int i = threadIdx.x; i < vec_per_chunk; i += 2 * blockDim.x) {
       const int i2 = i + blockDim.x;
       const bool has2 = i2 < vec_per_chunk;
-      float4 s0 = reinterpret_cast<const float4*>(mine + base)[i];
-      float4 s1 = has2 ? reinterpret_cast<const float4*>(mine + base)[i2] : make_float4(0.f, 0.f, 0.f, 0.f);
+      float4 s0 = ld_local_stream_f4(reinterpret_cast<const float4*>(mine + base) + i, pol);
+      float4 s1 = has2 ? ld_local_stream_f4(reinterpret_cast<const float4*>(mine + base) + i2, pol)
+                       : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll 2
       for (int p = 1; p < W; ++p) {
         const int peer = (rank + p) % W;   // stagger peers so that ranks do not all hit the same GPU at once
         const float4* src = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(grads.ptr[peer]) + base);
-        const float4 v0 = ld_relaxed_sys_f4(src + i);
+        const float4 v0 = ld_peer_stream_f4(src + i, pol);
         float4 v1 = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (has2) v1 = ld_relaxed_sys_f4(src + i2);
+        if (has2) v1 = ld_peer_stream_f4(src + i2, pol);
         s0.x += v0.x; s0.y += v0.y; s0.z += v0.z; s0.w += v0.w;
         s1.x += v1.x; s1.y += v1.y; s1.z += v1.z; s1.w += v1.w;
       }
-      reinterpret_cast<float4*>(mine + base)[i] = s0;
+      st_local_stream_f4(reinterpret_cast<float4*>(mine + base) + i, s0, pol);
       acc += s0.x * s0.x + s0.y * s0.y + s0.z * s0.z + s0.w * s0.w;
       if (has2) {
-        reinterpret_cast<float4*>(mine + base)[i2] = s1;
+        st_local_stream_f4(reinterpret_cast<float4*>(mine + base) + i2, s1, pol);
         acc += s1.x * s1.x + s1.y * s1.y + s1.z * s1.z + s1.w * s1.w;
       }
     }
@@ -301,9 +333,15 @@ extern "C" int hs_dp_reduce_scatter(void* const* grad_ptrs, void* const* sig_ptr
     set_last_error("hs_dp_reduce_scatter: bad arguments rank=%d W=%d chunks=[%lld,%lld) chunk=%d", rank, W, chunk_begin, chunk_end, chunk);
     return 1;
   }
+  // nblocks <= 0: one CTA per owned chunk (short-lived CTAs). What decides how well this kernel overlaps with
+  // backward turned out to be stream PRIORITY, not CTA lifetime: launched at a higher priority than the compute
+  // stream its pending CTAs took every SM slot freed at a GEMM kernel boundary and the next GEMM's CTAs (which
+  // need almost a whole SM each) waited; at a lower priority it only uses what backward leaves free.
   const long long owned = (chunk_end - chunk_begin + W - 1) / W;
-  int grid = nblocks > 0 ? nblocks : num_sms();
-  if (grid > owned) grid = static_cast<int>(owned < 1 ? 1 : owned);
+  long long want = nblocks > 0 ? nblocks : owned;
+  if (want > owned) want = owned;
+  if (want > 1 << 20) want = 1 << 20;
+  const int grid = static_cast<int>(want < 1 ? 1 : want);
   dp_reduce_scatter_kernel<<<grid, RS_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(g, s, rank, W, chunk_begin, chunk_end, chunk, slot, epoch, epoch_dev, sumsq_accum);
   return post_launch("dp_reduce_scatter_kernel");
 }

@@ -449,7 +449,11 @@ class Controller(object):
             self._graph = torch.cuda.CUDAGraph()
             self._capturing = True
             try:
-                with torch.cuda.graph(self._graph):
+                # capture on a HIGH-priority stream: kernel nodes inherit it, so at every kernel boundary the
+                # compute kernels' CTAs are placed before pending CTAs of the (default-priority) gradient
+                # reduce-scatter kernels, which then only use what backward leaves free
+                hp = torch.cuda.Stream(device=self.device, priority=-1)
+                with torch.cuda.graph(self._graph, stream=hp):
                     self._static_out = self._device_step([(self._static_sample, stats, False)], host_stats,
                                                          device_stats_sync=False)
             finally:
