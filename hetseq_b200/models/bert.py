@@ -3,17 +3,18 @@
 The module tree exists to give parameters the reference's state-dict names
 (``bert.encoder.layer.N.attention.self.query.weight`` ... ``cls.predictions.decoder.weight``,
 SURVEY.md section 2.2; 206 tensors / 110,106,428 params for BERT-base, 398 / 336,226,108 for
-BERT-large) -- checkpoints are interchangeable. The *computation* is written once, functionally, in
-``BertEncoderMath`` terms and has two interchangeable providers:
+BERT-large) -- checkpoints are interchangeable. The computation has two providers:
 
-* ``TorchOps``  (this file): plain PyTorch, fp32-exact restatement of the reference math -- GELU with
-  the constant 1.41421 (bert_modeling.py:104-106), TF-style LayerNorm with eps=1e-12 inside the sqrt
-  (:285-289), additive -10000 attention mask (:798-806), scores / sqrt(d) (:361-362), mean CE with
-  ignore_index=-1 (:881-886). It is the CPU path and the oracle for the GPU tests.
-* ``NativeOps`` (hetseq_b200/ops/bert_native.py): the sm_100a kernels -- one tcgen05 GEMM for the
-  packed QKV projection, fused attention, GEMM epilogues with bias/GELU, fused
-  dropout+residual+LayerNorm, gathered MLM head + fused cross-entropy -- selected automatically on
-  CUDA devices (``--kernels``).
+* the ``forward`` methods of the modules in this file: plain PyTorch, fp32-exact restatement of the
+  reference math -- GELU with the constant 1.41421 (bert_modeling.py:104-106), TF-style LayerNorm with
+  eps=1e-12 inside the sqrt (:285-289), additive -10000 attention mask (:798-806), scores / sqrt(d)
+  (:361-362), mean CE with ignore_index=-1 (:881-886). It is the CPU path, the ``--kernels torch`` path
+  and the oracle for the GPU tests.
+* ``hetseq_b200/ops/bert_native.py`` (attached to the model by ``attach()`` on CUDA devices with 16-bit
+  parameters, ``--kernels auto|native``): the sm_100a kernels -- one autograd node per encoder layer
+  (packed QKV tcgen05 GEMM, fused attention, GEMM epilogues with bias/GELU, fused
+  dropout+residual+LayerNorm), gathered MLM head + fused cross-entropy. ``BertLayer.forward``,
+  ``BertModel.forward`` and ``BertForPreTraining.forward`` hand over to it when it is attached.
 
 Deliberate deviations from the reference, all loss-preserving:
 * the MLM decoder and its cross-entropy run on the labelled rows only (<= 15 % of positions) instead
@@ -370,14 +371,20 @@ class BertPreTrainedModel(nn.Module):
             module.bias.data.zero_()
 
     @classmethod
-    def from_pretrained(cls, pretrained_model_name_or_path, state_dict=None, cache_dir=None, *inputs, **kwargs):
-        """Instantiate from a directory / archive holding ``bert_config.json`` + ``pytorch_model.bin``
-        (or a URL resolved through the download cache, hetseq_b200/utils/file_utils.py). Old
-        ``gamma``/``beta`` LayerNorm key names are renamed like bert_modeling.py:690-701."""
+    def from_pretrained(cls, pretrained_model_name_or_path, state_dict=None, cache_dir=None, from_tf=False,
+                        *inputs, **kwargs):
+        """Instantiate from a model name (PRETRAINED_MODEL_ARCHIVE_MAP), a directory or ``.tar.gz`` archive
+        holding ``bert_config.json`` + ``pytorch_model.bin``, or a URL resolved through the download cache
+        (hetseq_b200/utils/file_utils.py). ``from_tf`` reads a TensorFlow ``model.ckpt`` instead
+        (bert_modeling.py:43-101). Old ``gamma``/``beta`` LayerNorm key names are renamed like
+        bert_modeling.py:690-701."""
         from hetseq_b200.utils import file_utils
-        resolved = file_utils.resolve_archive(pretrained_model_name_or_path, cache_dir=cache_dir)
-        config = BertConfig.from_json_file(os.path.join(resolved, 'bert_config.json'))
+        resolved = file_utils.resolve_archive(pretrained_model_name_or_path, cache_dir=cache_dir,
+                                              archive_map=PRETRAINED_MODEL_ARCHIVE_MAP)
+        config = BertConfig.from_json_file(os.path.join(resolved, file_utils.CONFIG_NAME))
         model = cls(config, *inputs, **kwargs)
+        if from_tf:
+            return load_tf_weights_in_bert(model, os.path.join(resolved, file_utils.TF_WEIGHTS_NAME))
         if state_dict is None:
             state_dict = torch.load(os.path.join(resolved, 'pytorch_model.bin'), map_location='cpu',
                                     weights_only=True)
@@ -386,13 +393,99 @@ class BertPreTrainedModel(nn.Module):
             new_key = key.replace('gamma', 'weight').replace('beta', 'bias')
             renamed[new_key] = value
         own = model.state_dict()
-        prefix = '' if any(k.startswith('bert.') for k in renamed) or not hasattr(model, 'bert') else 'bert.'
-        loadable = {prefix + k: v for k, v in renamed.items() if prefix + k in own}
+        # a checkpoint of BertForPreTraining has 'bert.'-prefixed trunk keys, a bare BertModel checkpoint has
+        # none; either must load into either kind of model (bert_modeling.py:703-723 does this with a prefix walk)
+        loadable = {}
+        for key, value in renamed.items():
+            for cand in (key, 'bert.' + key, key[5:] if key.startswith('bert.') else None):
+                if cand is not None and cand in own and tuple(own[cand].shape) == tuple(value.shape):
+                    loadable[cand] = value
+                    break
         missing = [k for k in own if k not in loadable]
         model.load_state_dict(loadable, strict=False)
         if missing:
             print('| weights of {} not initialized from pretrained model: {}'.format(cls.__name__, missing))
         return model
+
+
+# short names accepted by from_pretrained (bert_modeling.py:33-41); resolved through the download cache
+_HF_S3 = 'https://s3.amazonaws.com/models.huggingface.co/bert/'
+PRETRAINED_MODEL_ARCHIVE_MAP = {name: _HF_S3 + name + '.tar.gz' for name in (
+    'bert-base-uncased', 'bert-large-uncased', 'bert-base-cased', 'bert-large-cased',
+    'bert-base-multilingual-uncased', 'bert-base-multilingual-cased', 'bert-base-chinese')}
+
+_TF_LEAF = {'kernel': 'weight', 'gamma': 'weight', 'beta': 'bias', 'bias': 'bias', 'output_bias': 'bias',
+            'output_weights': 'weight'}
+# TF scope names whose module has another name in this model tree (LinearActivation modules)
+_TF_RENAMES = (('intermediate/dense/', 'intermediate/dense_act/'), ('pooler/dense/', 'pooler/dense_act/'),
+               ('predictions/transform/dense/', 'predictions/transform/dense_act/'))
+
+
+def tf_variable_to_key(name: str):
+    """Google-BERT TensorFlow variable name -> (state-dict key, transpose?) or None for optimizer slots.
+
+    ``bert/encoder/layer_3/attention/self/query/kernel`` -> (``bert.encoder.layer.3.attention.self.query.weight``,
+    True): dense kernels are stored [in, out] in TF and [out, in] here (bert_modeling.py:66-101 walks the
+    module tree attribute by attribute; this is the same mapping as a pure function, so it can be tested
+    without TensorFlow)."""
+    parts = name.split('/')
+    if any(p in ('adam_v', 'adam_m', 'global_step') or p.startswith('AdamWeightDecayOptimizer') for p in parts):
+        return None
+    name = name + '/'
+    for old, new in _TF_RENAMES:
+        name = name.replace(old, new)
+    parts = name.rstrip('/').split('/')
+    leaf = parts[-1]
+    out = []
+    for p in parts[:-1]:
+        head, sep, num = p.rpartition('_')
+        if sep and num.isdigit() and head.isalpha():
+            out += [head, num]          # layer_7 -> layer.7
+        else:
+            out.append(p)
+    if leaf.endswith('_embeddings'):
+        return '.'.join(out + [leaf, 'weight']), False
+    if parts[-2:] == ['predictions', 'output_bias']:
+        return '.'.join(out + ['bias']), False
+    if leaf not in _TF_LEAF:
+        raise KeyError('unrecognised TensorFlow variable {}'.format(name.rstrip('/')))
+    return '.'.join(out + [_TF_LEAF[leaf]]), leaf == 'kernel'
+
+
+def load_tf_weights_in_bert(model, tf_checkpoint_path, reader=None):
+    """Copy a TensorFlow BERT checkpoint into ``model`` (bert_modeling.py:43-101). ``reader`` (tests) is an
+    iterable of (variable name, numpy array); by default the checkpoint is read with TensorFlow, which is
+    imported only here."""
+    import numpy as np
+    if reader is None:
+        try:
+            import tensorflow as tf
+        except ImportError:
+            print('Loading a TensorFlow model in PyTorch requires TensorFlow to be installed.')
+            raise
+        path = os.path.abspath(tf_checkpoint_path)
+        reader = ((n, tf.train.load_variable(path, n)) for n, _ in tf.train.list_variables(path))
+    own = model.state_dict()
+    loaded = set()
+    for name, array in reader:
+        mapped = tf_variable_to_key(name)
+        if mapped is None:
+            continue
+        key, transpose = mapped
+        if key not in own and hasattr(model, 'bert') and not key.startswith(('bert.', 'cls.')):
+            key = 'bert.' + key
+        if key not in own:
+            raise KeyError('TensorFlow variable {} maps to {}, which this model does not have'.format(name, key))
+        array = np.asarray(array)
+        if transpose:
+            array = array.T
+        if tuple(own[key].shape) != tuple(array.shape):
+            raise ValueError('shape mismatch for {}: checkpoint {} vs model {}'.format(key, array.shape,
+                                                                                      tuple(own[key].shape)))
+        with torch.no_grad():
+            own[key].copy_(torch.from_numpy(np.ascontiguousarray(array)))
+        loaded.add(key)
+    return model
 
 
 def extended_attention_mask(attention_mask, dtype):
