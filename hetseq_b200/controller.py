@@ -29,7 +29,7 @@ import torch
 from hetseq_b200 import registry
 from hetseq_b200.parallel import data_parallel, distributed_utils
 from hetseq_b200.parallel.flat_buffer import FlatParamBuffer
-from hetseq_b200.utils import checkpoint_utils
+from hetseq_b200.utils import checkpoint_utils, nvtx
 from hetseq_b200.utils.meters import AverageMeter, CudaEventTimer, StopwatchMeter, TimeMeter
 
 
@@ -63,6 +63,7 @@ class Controller(object):
         self.step_timer = CudaEventTimer(use_cuda=self.cuda)
         # HETSEQ_PHASE_TIMING=1: CUDA-event timing of the phases of every update (printed by close())
         self._phase_timing = self.cuda and bool(int(os.environ.get('HETSEQ_PHASE_TIMING', '0')))
+        nvtx.enable(getattr(args, 'profile_nvtx', False) and self.cuda)
         self._phase_events = []
         # --cuda-graph: capture the device part of an update once, replay it afterwards
         self._graph_enabled = bool(getattr(args, 'cuda_graph', False)) and self.cuda
@@ -331,6 +332,10 @@ class Controller(object):
         try:
             opt.finish_update(bool(skip) and opt.scaler is not None)
             self.set_num_updates(self.get_num_updates() + 1)
+            every = int(getattr(self.args, 'check_params_interval', 0) or 0)
+            if every > 0 and self._num_updates % every == 0 and not self.dp.check_params_consistent():
+                raise RuntimeError('Fatal error: parameters differ between workers after update {}'.format(
+                    self._num_updates))
             self.task.update_step(self._num_updates)
             self._prev_grad_norm = gnorm
             # like the fast path of the reference (controller.py:299-304) losses are logged as
@@ -369,14 +374,17 @@ class Controller(object):
         dp.begin_update(len(prepared))
         for i, (sample_dev, stats, ignore_grad) in enumerate(prepared):
             dp.begin_micro_batch(i, is_last=(i == len(prepared) - 1))
-            loss, sample_size, logging_output = self.task.train_step(sample_dev, model, opt, ignore_grad, stats=stats)
+            with nvtx.range('fwd+bwd micro-batch'):
+                loss, sample_size, logging_output = self.task.train_step(sample_dev, model, opt, ignore_grad,
+                                                                         stats=stats)
             if not ignore_grad:
                 weight = logging_output.get('nsentences', 1) if self.args.sample_size_mode == 'batch' else 1.0
                 loss_sum = loss_sum + logging_output['loss'].float() * weight
         if marks is not None:
             marks.append(self._mark())      # forward + backward enqueued
         opt.buffer.finalize_grads()
-        dp.finish_gradients(opt)
+        with nvtx.range('gradient reduction (exposed part)'):
+            dp.finish_gradients(opt)
         if marks is not None:
             marks.append(self._mark())      # gradient reduction complete
 
@@ -419,10 +427,12 @@ class Controller(object):
         # over ranks, so the factor is world / sample_size like the reference's
         opt.multiply_grads(torch.where(sample_size_dev > 0, world / sample_size_dev.clamp(min=1e-12),
                                        torch.ones_like(sample_size_dev)).float())
-        grad_norm = opt.clip_grad_norm(self.args.clip_norm)
+        with nvtx.range('grad norm + clip'):
+            grad_norm = opt.clip_grad_norm(self.args.clip_norm)
         if marks is not None:
             marks.append(self._mark())      # stats sync + norm
-        opt.launch_update()
+        with nvtx.range('optimizer update (+ all-gather)'):
+            opt.launch_update()
         if marks is not None:
             marks.append(self._mark())      # update (+ all-gather)
             self._phase_events.append(marks)

@@ -28,6 +28,7 @@ import torch
 import torch.nn.functional as F
 
 from hetseq_b200.ops import lib, native, rng
+from hetseq_b200.utils import nvtx
 from hetseq_b200.ops.native import (ACT_ADD_AUX, ACT_DGELU_MUL, ACT_GELU, ACT_GELU_DAUX, ACT_MUL_AUX, ACT_NONE,
                                     ACT_TANH)
 
@@ -204,6 +205,22 @@ class EncoderLayerFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, add_mask, anchor, nb, layer, training):
+        nvtx.push('encoder layer fwd')
+        try:
+            return EncoderLayerFn._forward(ctx, x, add_mask, anchor, nb, layer, training)
+        finally:
+            nvtx.pop()
+
+    @staticmethod
+    def backward(ctx, dx2):
+        nvtx.push('encoder layer bwd')
+        try:
+            return EncoderLayerFn._backward(ctx, dx2)
+        finally:
+            nvtx.pop()
+
+    @staticmethod
+    def _forward(ctx, x, add_mask, anchor, nb, layer, training):
         L = lib.load()
         B, S = nb._bs
         H, I, heads = nb.H, nb.I, nb.heads
@@ -243,7 +260,7 @@ class EncoderLayerFn(torch.autograd.Function):
         return x2
 
     @staticmethod
-    def backward(ctx, dx2):
+    def _backward(ctx, dx2):
         x, add_mask, qkv, ctxv, lse, z1, mean1, rstd1, x1, dact, h, z2, mean2, rstd2 = ctx.saved_tensors
         nb, layer, p_attn, p_h, B, S = ctx.meta
         L = lib.load()

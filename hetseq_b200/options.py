@@ -93,6 +93,9 @@ def add_general_args(parser):
                        help='capture forward+backward+update of a step in a CUDA graph and replay it')
     group.add_argument('--profile-nvtx', action='store_true',
                        help='emit NVTX ranges per phase (forward/backward/reduce/update)')
+    group.add_argument('--check-params-interval', type=int, default=0, metavar='N',
+                       help='every N updates verify that all ranks hold bit-identical parameters (debug aid for '
+                            'the in-kernel gradient path; replaces the grad-norm equality assert of the reference)')
     return parser
 
 
