@@ -20,6 +20,7 @@
 #include "host.h"
 #include "../include/hetseq_b200.h"
 
+#include <cstdlib>
 #include <type_traits>
 
 namespace hs {
@@ -424,6 +425,19 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
 constexpr int ATTN_FWD_SMEM = 3 * TILE_BYTES + PBUF_BYTES + 3 * AT_S * 4 + 64 + 1024;
 constexpr int ATTN_BWD_SMEM = 4 * TILE_BYTES + PBUF_BYTES + AT_S * 4 + 3 * AT_D * 4 + 64 + 1024;
 
+// multi-tile kernels (attention_multi_sm100.cu): S = 256, 384, 512
+bool attn_multi_supported(int S, int head_dim);
+int attn_multi_fwd(const void* qkv, const float* mask, void* ctx, float* lse, int B, int S, int heads, int H,
+                   float dropout_p, const long long* seed, unsigned site, int dtype, cudaStream_t s);
+int attn_multi_bwd(const void* qkv, const float* mask, const void* ctx, const void* dctx, const float* lse,
+                   void* dqkv, float* dbias, int B, int S, int heads, int H, float dropout_p, const long long* seed,
+                   unsigned site, int dtype, cudaStream_t s);
+// HETSEQ_ATTN_MULTI=0 keeps sequence lengths other than 128 on the caller's composite path
+static bool multi_enabled() {
+  static const bool on = [] { const char* e = getenv("HETSEQ_ATTN_MULTI"); return e == nullptr || atoi(e) != 0; }();
+  return on;
+}
+
 static int attn_check(const char* who, int B, int S, int heads, int H) {
   if (S != AT_S || heads <= 0 || H != heads * AT_D || B <= 0) {
     set_last_error("%s: unsupported shape B=%d S=%d heads=%d H=%d (needs S=%d, head_dim=%d)", who, B, S, heads, H, AT_S, AT_D);
@@ -436,13 +450,18 @@ static int attn_check(const char* who, int B, int S, int heads, int H) {
 
 using namespace hs;
 
-extern "C" int hs_attention_supported(int S, int head_dim) { return (S == AT_S && head_dim == AT_D) ? 1 : 0; }
+extern "C" int hs_attention_supported(int S, int head_dim) {
+  if (S == AT_S && head_dim == AT_D) return 1;
+  return (multi_enabled() && attn_multi_supported(S, head_dim)) ? 1 : 0;
+}
 
 extern "C" int hs_attention_fwd(const void* qkv, const float* mask, void* ctx, float* lse, int B, int S, int heads,
                                 int H, float dropout_p, const long long* seed, unsigned site, int dtype,
                                 hs_stream_t stream) {
-  if (attn_check("hs_attention_fwd", B, S, heads, H)) return 1;
   if (dropout_p > 0.f && seed == nullptr) { set_last_error("hs_attention_fwd: dropout needs a seed pointer"); return 1; }
+  if (S != AT_S && heads > 0 && B > 0 && H == heads * AT_D && attn_multi_supported(S, AT_D))
+    return attn_multi_fwd(qkv, mask, ctx, lse, B, S, heads, H, dropout_p, seed, site, dtype, static_cast<cudaStream_t>(stream));
+  if (attn_check("hs_attention_fwd", B, S, heads, H)) return 1;
   CUtensorMap tm;
   if (make_tmap_2d_16b(&tm, qkv, 3ull * H, static_cast<uint64_t>(B) * S, 3ull * H, 64, AT_S)) return 1;
   AttnParams P{mask, ctx, nullptr, nullptr, lse, nullptr, B, heads, H, 0.125f, dropout_p, seed, site};
@@ -464,9 +483,15 @@ extern "C" int hs_attention_bwd(const void* qkv, const float* mask, const void* 
                                 void* dqkv, float* dbias, int accumulate_bias, int B, int S, int heads, int H,
                                 float dropout_p, const long long* seed, unsigned site, int dtype,
                                 hs_stream_t stream) {
-  if (attn_check("hs_attention_bwd", B, S, heads, H)) return 1;
+  const bool multi = S != AT_S && heads > 0 && B > 0 && H == heads * AT_D && attn_multi_supported(S, AT_D);
+  if (!multi && attn_check("hs_attention_bwd", B, S, heads, H)) return 1;
   if (dbias != nullptr && !accumulate_bias)
     HS_CUDA_OK(cudaMemsetAsync(dbias, 0, sizeof(float) * 3 * H, static_cast<cudaStream_t>(stream)));
+  if (multi) {
+    if (dropout_p > 0.f && seed == nullptr) { set_last_error("hs_attention_bwd: dropout needs a seed pointer"); return 1; }
+    return attn_multi_bwd(qkv, mask, ctx, dctx, lse, dqkv, dbias, B, S, heads, H, dropout_p, seed, site, dtype,
+                          static_cast<cudaStream_t>(stream));
+  }
   if (dropout_p > 0.f && seed == nullptr) { set_last_error("hs_attention_bwd: dropout needs a seed pointer"); return 1; }
   CUtensorMap tmQ, tmD;
   if (make_tmap_2d_16b(&tmQ, qkv, 3ull * H, static_cast<uint64_t>(B) * S, 3ull * H, 64, AT_S)) return 1;

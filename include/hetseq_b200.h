@@ -175,7 +175,9 @@ HS_API int hs_colsum_rows_where(const void* x, const void* sel, int sel_i64, lon
                                 int accumulate, float* scratch, int dtype, hs_stream_t stream);
 
 /* ---- fused attention on tcgen05 (csrc/attention_sm100.cu; bert_modeling.py:351-377, K2-K4/W4) -------- */
-/* 1 when the fused kernel handles this (sequence length, head dim); callers must check first. */
+/* 1 when the fused kernels handle this (sequence length, head dim): head dim 64 and S = 128 (single-tile
+ * kernels) or S = 256 / 384 / 512 (multi-tile kernels, attention_multi_sm100.cu; HETSEQ_ATTN_MULTI=0 disables
+ * them). Callers must check first. */
 HS_API int hs_attention_supported(int S, int head_dim);
 /* ctx[M,H] = merge_heads(dropout(softmax(Q K^T / sqrt(d) + mask)) V) from the packed projection
  * qkv [M, 3H] (q | k | v column blocks, heads of 64 inside each). mask: [B,S] additive fp32.

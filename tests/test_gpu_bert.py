@@ -42,15 +42,16 @@ def _batch(vocab=2000, B=8, S=128):
     return SyntheticBertData(B, S, 10, vocab, seed=3).fetch_rows(list(range(B)))
 
 
-@pytest.mark.parametrize('flag', ['--fp16', '--bf16'])
-def test_native_loss_and_grads_match_torch(tmp_path, flag):
-    """Same 16-bit weights, dropout off: native loss/gradients vs an fp32 PyTorch model."""
-    ctl, task = _build(str(tmp_path), flag, 'native')
+@pytest.mark.parametrize('flag,S', [('--fp16', 128), ('--bf16', 128), ('--fp16', 256)])
+def test_native_loss_and_grads_match_torch(tmp_path, flag, S):
+    """Same 16-bit weights, dropout off: native loss/gradients vs an fp32 PyTorch model. S = 256 goes through the
+    multi-tile attention kernels inside the fused encoder-layer node."""
+    ctl, task = _build(str(tmp_path), flag, 'native', max_position_embeddings=max(128, S))
     assert ctl.get_model().native is not None, 'native kernels were not attached'
     from hetseq_b200.models.bert import BertConfig, BertForPreTraining
     ref = BertForPreTraining(BertConfig.from_json_file(os.path.join(str(tmp_path), 'cfg.json'))).cuda().float()
     ref.load_state_dict({k: v.float() for k, v in ctl.get_model().state_dict().items()})
-    sample = _batch()
+    sample = _batch(S=S)
     dev = task.prepare_sample(sample, ctl.device)
     ctl.get_model().train()
     ctl.zero_grad()

@@ -322,15 +322,17 @@ def _attn_ref(qkv, mask, B, S, heads):
 
 
 @pytest.mark.parametrize('dt', DT)
-def test_attention_fwd_bwd(dt):
+@pytest.mark.parametrize('S', [128, 256, 512])
+def test_attention_fwd_bwd(dt, S):
+    """S = 128: single-tile kernels; S = 256 / 512: multi-tile kernels (two-pass forward, dK/dV and dQ backward)."""
     from hetseq_b200.ops import attention_native as an
-    B, S, heads, d = 3, 128, 4, 64
+    B, heads, d = 3, 4, 64
     H = heads * d
     assert an.supports(B, S, heads, d, dt)
     torch.manual_seed(8)
     qkv = (torch.randn(B * S, 3 * H, device='cuda') * 0.7).to(dt).requires_grad_(True)
     mask = torch.zeros(B, S, device='cuda')
-    mask[0, 100:] = -10000.0
+    mask[0, S - 28:] = -10000.0
     mask[2, 17:] = -10000.0
     out = an.attention(qkv, mask, B, S, heads, 0.0, 1)
     ref_in = qkv.detach().float().requires_grad_(True)
@@ -361,11 +363,12 @@ def test_attention_fwd_bwd(dt):
     torch.testing.assert_close(dbias, ref_in.grad.sum(0) + 1.5, rtol=2e-2, atol=0.05 if dt == torch.float16 else 0.3)
 
 
-def test_attention_dropout_consistency():
+@pytest.mark.parametrize('S', [128, 384])
+def test_attention_dropout_consistency(S):
     """Dropout: same (seed, site) -> identical output; backward uses the very same mask (checked through
     linearity: with V = ones-like structure the gradient of sum(out) w.r.t. v equals column sums of P_drop)."""
     from hetseq_b200.ops import attention_native as an, rng
-    B, S, heads, d = 2, 128, 2, 64
+    B, heads, d = 2, 2, 64
     H = heads * d
     dt = torch.float16
     torch.manual_seed(9)
