@@ -14,8 +14,9 @@
 //             times through different UMMA descriptors (K-major for dQ = dS K, MN-major for
 //             dV = P^T dO and dK = dS^T Q) -> dQ,dK,dV written into the packed [M,3H] gradient.
 //
-// The score matrix never leaves the SM. Sequence length 128 per tile (BERT phase 1); other lengths
-// are reported as unsupported by hs_attention_supported() and the caller must not use this kernel.
+// The score matrix never leaves the SM. This file holds the single-tile kernels (sequence length 128, BERT
+// phase 1); sequence lengths of 2..4 tiles are handled by attention_multi_sm100.cu, to which the host entry
+// points below dispatch. Anything else is reported as unsupported by hs_attention_supported().
 #include "common.cuh"
 #include "host.h"
 #include "../include/hetseq_b200.h"
