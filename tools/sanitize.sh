@@ -4,6 +4,8 @@
 # gemm    : the stand-alone GEMM harness (no Python), numerics cases only
 # kernels : tests/test_gpu_kernels.py (every kernel against its PyTorch oracle)
 # bert    : one end-to-end native BERT test
+# NOTE: on the shared B200 pool used for this project compute-sanitizer is closed by the operators (the wrapper
+# refuses to start it); the script is kept for boxes where it is available.
 # Output goes to gpurun_out/sanitize_<tool>_<target>.log; the exit code is the sanitizer's (non-zero on findings).
 set -e
 TOOL=${1:-memcheck}
