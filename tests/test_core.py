@@ -227,3 +227,47 @@ def test_eval_mnist_cli(tmp_path, capsys):
     loss, acc = eval_mnist.main(['--model_ckpt', os.path.join(a.save_dir, 'checkpoint_last.pt'), '--mnist_dir',
                                  str(tmp_path / 'data'), '--device', 'cpu'])
     assert 'Test set: Average loss' in capsys.readouterr().out and acc > 0.5
+
+
+def test_flat_buffer_lazy_zero_grad_and_finalize():
+    """16-bit parameters + fp32 main gradients: zero_grad() does not clear the big views (their first write of a
+    window overwrites), small parameters are cleared eagerly, and finalize_grads() zeroes whatever got no gradient
+    -- so a parameter that is unused in one update does not keep the previous update's gradient."""
+    import torch
+    from hetseq_b200.parallel.flat_buffer import SMALL_PARAM_NUMEL, FlatParamBuffer
+    torch.manual_seed(0)
+    big = torch.nn.Parameter(torch.randn(SMALL_PARAM_NUMEL + 64, dtype=torch.bfloat16))
+    unused = torch.nn.Parameter(torch.randn(SMALL_PARAM_NUMEL + 8, dtype=torch.bfloat16))
+    small = torch.nn.Parameter(torch.randn(16, dtype=torch.bfloat16))
+    buf = FlatParamBuffer([big, unused, small])
+    ready = []
+    buf.ready_callback = ready.append
+
+    def step(use_unused):
+        buf.zero_grad()
+        loss = (big.float() * 2).sum() + (small.float() * 3).sum()
+        if use_unused:
+            loss = loss + (unused.float() * 5).sum()
+        loss.backward()
+        buf.finalize_grads()
+
+    step(True)
+    assert torch.all(big.main_grad == 2) and torch.all(unused.main_grad == 5) and torch.all(small.main_grad == 3)
+    # stale values are still in the buffer after zero_grad (no memset) ...
+    buf.zero_grad()
+    assert torch.all(big.main_grad == 2) and torch.all(small.main_grad == 0)
+    assert buf._written == [False, False, True]
+    # ... but an update that does not touch `unused` ends with zeros there, not with the old 5s
+    ready.clear()
+    step(False)
+    assert torch.all(big.main_grad == 2) and torch.all(unused.main_grad == 0) and torch.all(small.main_grad == 3)
+    assert 1 in ready          # finalize_grads reported the unused parameter ready
+    # accumulation over two micro-batches inside one window adds
+    buf.zero_grad()
+    for _ in range(2):
+        ((big.float() * 2).sum() + (small.float() * 3).sum()).backward()
+    buf.finalize_grads()
+    assert torch.all(big.main_grad == 4) and torch.all(small.main_grad == 6)
+    # padding between parameters is never written
+    end_big = buf.offsets[0] + buf.numels[0]
+    assert torch.all(buf.flat_grad[end_big:buf.offsets[1]] == 0)
