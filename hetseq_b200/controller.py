@@ -31,6 +31,7 @@ from hetseq_b200.parallel import data_parallel, distributed_utils
 from hetseq_b200.parallel.flat_buffer import FlatParamBuffer
 from hetseq_b200.utils import checkpoint_utils, nvtx
 from hetseq_b200.utils.meters import AverageMeter, CudaEventTimer, StopwatchMeter, TimeMeter
+from hetseq_b200.utils.utils import PackedSample
 
 
 class Controller(object):
@@ -68,6 +69,7 @@ class Controller(object):
         # --cuda-graph: capture the device part of an update once, replay it afterwards
         self._graph_enabled = bool(getattr(args, 'cuda_graph', False)) and self.cuda
         self._graph, self._graph_key, self._graph_warmup, self._capturing = None, None, 0, False
+        self._static_sample = None
         self._static_sample, self._static_out = None, None
         self._stats_host = None
         self.init_meters(args)
@@ -291,8 +293,9 @@ class Controller(object):
 
         # ---- host -> device ---------------------------------------------------------------------
         prepared, host_stats = [], [0, 0, 0]          # sample_size, nsentences, ntokens
+        allow_host = self._graph_enabled and not dummy_batch and len(samples) == 1
         for sample in samples:
-            p = self._prepare_sample(sample)
+            p = self._prepare_sample(sample, allow_host)
             ignore = p is None
             if ignore:
                 # uneven shards: run on the cached dummy batch and ignore its gradients so that every rank
@@ -447,6 +450,7 @@ class Controller(object):
         sample_dev, stats, _ = prepared_one
         key = tuple((tuple(t.shape), t.dtype) for t in sample_dev) + (tuple(host_stats[:2]),)
         if self._graph is not None and key != self._graph_key:
+            prepared_one = (self.task.prepare_sample(sample_dev, self.device), stats, False)
             return self._device_step([prepared_one], host_stats, device_stats_sync=True)   # odd-shaped batch: eager
         if self._graph is None:
             self._graph_warmup += 1
@@ -454,7 +458,11 @@ class Controller(object):
                 return self._device_step([prepared_one], host_stats, device_stats_sync=True)
             # capture
             self._graph_key = key
-            self._static_sample = [t.clone() for t in sample_dev]
+            if isinstance(sample_dev, PackedSample):
+                sample_dev = sample_dev.to(self.device)
+                self._static_sample = sample_dev.clone()
+            else:
+                self._static_sample = [t.clone() for t in sample_dev]
             torch.cuda.synchronize()
             self._graph = torch.cuda.CUDAGraph()
             self._capturing = True
@@ -469,8 +477,12 @@ class Controller(object):
             finally:
                 self._capturing = False
             # the captured update was only recorded, not executed: fall through to a replay
-        for dst, src in zip(self._static_sample, sample_dev):
-            dst.copy_(src, non_blocking=True)
+        if isinstance(self._static_sample, PackedSample) and self._static_sample.same_layout(sample_dev):
+            # ONE copy (host-pinned -> static buffer directly when the batch was left on the host, else D2D)
+            self._static_sample.flat.copy_(sample_dev.flat, non_blocking=True)
+        else:
+            for dst, src in zip(self._static_sample, sample_dev):
+                dst.copy_(src, non_blocking=True)
         self.optimizer.write_host_scalars()
         self._stats_host[0], self._stats_host[1], self._stats_host[4] = host_stats[0], host_stats[1], host_stats[2]
         self._graph.replay()
@@ -515,11 +527,17 @@ class Controller(object):
         self._num_updates = num_updates
         self.lr_step_update()
 
-    def _prepare_sample(self, sample):
-        """Returns (device sample, host stats) or None for an empty (padding) batch."""
+    def _prepare_sample(self, sample, allow_host: bool = False):
+        """Returns (device sample, host stats) or None for an empty (padding) batch. With ``allow_host`` a pinned
+        packed batch that matches the captured graph's inputs is left on the host: the replay path copies it
+        straight into the graph's static buffers."""
         if sample is None or len(sample) == 0:
             return None
         stats = self.task.sample_stats(sample)
+        if (allow_host and self._graph is not None and isinstance(sample, PackedSample) and sample.flat.device.type == 'cpu'
+                and sample.flat.is_pinned() and self._static_sample is not None
+                and isinstance(self._static_sample, PackedSample) and self._static_sample.same_layout(sample)):
+            return sample, stats        # goes host -> static graph inputs in one copy (_graphed_device_step)
         return self.task.prepare_sample(sample, self.device), stats
 
     def _set_seed(self):

@@ -92,6 +92,9 @@ class EpochBatchIterator(object):
         self.epoch = epoch
         self._cur_epoch_itr = None
         self._next_epoch_itr = None
+        #: set by a PrefetchIterator that reads ahead of the trainer: callable(counting_iterator) -> number of
+        #: batches the TRAINER has consumed (the raw count includes batches still waiting in the prefetch queue)
+        self.position_hook = None
 
     def __len__(self):
         return len(self.frozen_batches)
@@ -109,11 +112,16 @@ class EpochBatchIterator(object):
         return self._cur_epoch_itr
 
     def end_of_epoch(self) -> bool:
-        return not self._cur_epoch_itr.has_next()
+        if self._cur_epoch_itr.has_next():
+            return False
+        # exhausted by a prefetcher does not mean trained: batches may still sit in its queue
+        return self.position_hook is None or self.position_hook(self._cur_epoch_itr) >= self._cur_epoch_itr.count
 
     @property
     def iterations_in_epoch(self):
         if self._cur_epoch_itr is not None:
+            if self.position_hook is not None:
+                return self.position_hook(self._cur_epoch_itr)
             return self._cur_epoch_itr.count
         if self._next_epoch_itr is not None:
             return self._next_epoch_itr.count
@@ -213,11 +221,18 @@ class PrefetchIterator(object):
 
     _END = object()
 
-    def __init__(self, iterable, depth=2, pin_memory: Optional[bool] = None):
+    def __init__(self, iterable, depth=2, pin_memory: Optional[bool] = None, transform=None):
         self.iterable = iterable
+        #: optional callable applied to every item in the worker thread (e.g. Task.host_prepare on each
+        #: micro-batch of a GroupedIterator chunk): host-side batch preparation then overlaps with the GPU
+        self.transform = transform
         self.pin = torch.cuda.is_available() if pin_memory is None else pin_memory
         self.q: queue.Queue = queue.Queue(maxsize=max(1, depth))
         self._err = None
+        # batches handed to the consumer so far (a GroupedIterator chunk counts as len(chunk)); only the consumer
+        # thread touches these, so no lock is needed
+        self._handed = 0
+        self._base = 0
         self.offset = getattr(iterable, 'offset', 0)
         self._thread = threading.Thread(target=self._worker, daemon=True)
         self._started = False
@@ -230,6 +245,9 @@ class PrefetchIterator(object):
         return getattr(self.iterable, 'count', 0)
 
     def _pin(self, x):
+        from hetseq_b200.utils.utils import PackedSample
+        if isinstance(x, PackedSample):      # one flat buffer: pin that, keep the views consistent
+            return x if x.flat.is_pinned() else PackedSample(x.flat.pin_memory(), x.shapes)
         if torch.is_tensor(x):
             return x.pin_memory() if (x.device.type == 'cpu' and not x.is_pinned()) else x
         if isinstance(x, dict):
@@ -238,9 +256,29 @@ class PrefetchIterator(object):
             return type(x)(self._pin(v) for v in x)
         return x
 
+    @staticmethod
+    def _size(item) -> int:
+        return len(item) if isinstance(item, (list, tuple)) else 1
+
+    def consumed_count(self, counter=None) -> int:
+        """Position of the CONSUMER in the epoch: where the underlying CountingIterator stood when this prefetcher
+        was attached plus the batches handed out since. The raw count of that iterator also includes batches
+        still waiting in the queue, which a mid-epoch checkpoint must not skip on resume."""
+        return self._base + self._handed
+
+    def attach_to(self, epoch_itr) -> 'PrefetchIterator':
+        """Make ``epoch_itr.state_dict()`` / ``end_of_epoch()`` see the trainer's position, not the reader's.
+        Call before the first ``next()`` (the worker thread has not pulled anything yet)."""
+        assert not self._started, 'attach_to() must be called before iteration starts'
+        self._base = getattr(epoch_itr._cur_epoch_itr, 'count', 0)     # the resume offset, or 0
+        epoch_itr.position_hook = self.consumed_count
+        return self
+
     def _worker(self):
         try:
             for item in self.iterable:
+                if self.transform is not None:
+                    item = self.transform(item)
                 self.q.put(self._pin(item) if self.pin else item)
         except BaseException as e:  # surfaced in the consumer thread
             self._err = e
@@ -259,4 +297,5 @@ class PrefetchIterator(object):
             if self._err is not None:
                 raise self._err
             raise StopIteration
+        self._handed += self._size(item)
         return item

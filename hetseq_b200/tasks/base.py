@@ -97,6 +97,12 @@ class Task(object):
             return len(sample[0][0])
         return nsentences
 
+    def host_prepare(self, sample):
+        """CPU-side part of ``prepare_sample`` (dtype narrowing, index building, pinning). Safe to run in the
+        prefetch thread, one update ahead of the GPU (``data/iterators.py::PrefetchIterator(transform=...)``);
+        ``prepare_sample`` must accept its output. Default: nothing to do."""
+        return sample
+
     def prepare_sample(self, sample, device):
         """Host -> device hand-off for one collated micro-batch."""
         from hetseq_b200.utils import utils

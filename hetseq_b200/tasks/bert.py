@@ -115,12 +115,36 @@ class LanguageModelingTask(Task):
         kernels consume int32 directly; PyTorch-path modules widen as needed. Appends
         the host-computed MLM row index (see ``mlm_index``) unless ``--mlm-all-positions``."""
         from hetseq_b200.utils import utils
+        cuda = torch.device(device).type == 'cuda'
+        sample = self._host_part(sample, narrow=cuda)
+        if cuda and not isinstance(sample, utils.PackedSample):
+            sample = utils.PackedSample.pack(sample, pin=True) or sample     # one H2D copy instead of seven
+        return utils.move_to_device(sample, device)
+
+    def _host_part(self, sample, narrow):
+        from hetseq_b200.utils import utils
+        if isinstance(sample, utils.PackedSample):
+            return sample                    # already prepared by host_prepare()
         sample = list(sample)
         if len(sample) == 5 and sample[3].device.type == 'cpu' and not getattr(self.args, 'mlm_all_positions', False):
             sample += list(self.mlm_index(sample[3]))
-        if torch.device(device).type == 'cuda':
+        if narrow:
             sample = [t.to(torch.int32) if t.dtype == torch.int64 else t for t in sample]
-        return utils.move_to_device(sample, device)
+        return sample
+
+    def host_prepare(self, sample):
+        """Everything of ``prepare_sample`` that does not need the device: the MLM row index, int64 -> int32 and
+        pinning, so that only the (asynchronous) copies are left for the training thread."""
+        if sample is None or len(sample) == 0:
+            return sample
+        from hetseq_b200.utils import utils
+        cuda = torch.cuda.is_available() and not getattr(self.args, 'cpu', False)
+        sample = self._host_part(sample, narrow=cuda)
+        if cuda and not isinstance(sample, utils.PackedSample):
+            packed = utils.PackedSample.pack(sample, pin=True)     # all int32 after narrowing: one pinned buffer
+            sample = packed if packed is not None else \
+                [t.pin_memory() if (t.device.type == 'cpu' and not t.is_pinned()) else t for t in sample]
+        return sample
 
 
 @register_task('bert_token_classification')

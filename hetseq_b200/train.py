@@ -114,6 +114,13 @@ def train(args, controller, task, epoch_itr):
     itr = epoch_itr.next_epoch_itr(fix_batches_to_gpus=args.fix_batches_to_gpus,
                                    shuffle=(epoch_itr.epoch >= args.curriculum))
     itr = iterators.GroupedIterator(itr, update_freq)
+    if controller.cuda or os.environ.get('HETSEQ_PREFETCH', '') == '1':
+        # batch preparation (MLM row index, int32 narrowing, pinning) runs one update ahead in a background
+        # thread; the training thread is left with the asynchronous host->device copies
+        itr = iterators.PrefetchIterator(itr, depth=2, transform=lambda chunk: [task.host_prepare(s) for s in chunk])
+        itr.attach_to(epoch_itr)
+    else:
+        epoch_itr.position_hook = None
     progress = progress_bar.build_progress_bar(args, itr, epoch_itr.epoch, no_progress_bar='simple')
 
     extra_meters = collections.defaultdict(lambda: AverageMeter())

@@ -34,6 +34,53 @@ def apply_to_sample(f, sample):
     return _apply(sample)
 
 
+class PackedSample(list):
+    """A micro-batch whose tensors are views of ONE flat buffer (``.flat``), so that it crosses PCIe -- and is
+    copied into the static input buffers of a captured CUDA graph -- as a single copy instead of one per tensor
+    (a BERT batch is 7 small int32 tensors: the per-copy latency, not the 70 KB, was what the step waited for).
+    Behaves like the plain list of tensors everywhere else."""
+
+    ALIGN = 4      # elements; keeps every view 16-byte aligned for 4-byte dtypes
+
+    def __init__(self, flat: torch.Tensor, shapes):
+        self.flat = flat
+        self.shapes = [tuple(s) for s in shapes]
+        views, off = [], 0
+        for shp in self.shapes:
+            n = 1
+            for d in shp:
+                n *= d
+            views.append(flat[off:off + n].view(shp))
+            off += (n + self.ALIGN - 1) // self.ALIGN * self.ALIGN
+        super().__init__(views)
+
+    @classmethod
+    def pack(cls, tensors, pin: bool = False):
+        """Pack CPU tensors of one common dtype; returns None when they cannot be packed."""
+        tensors = list(tensors)
+        if not tensors or any((not torch.is_tensor(t)) or t.device.type != 'cpu' or t.dtype != tensors[0].dtype
+                              for t in tensors):
+            return None
+        total = sum((t.numel() + cls.ALIGN - 1) // cls.ALIGN * cls.ALIGN for t in tensors)
+        flat = torch.zeros(total, dtype=tensors[0].dtype, pin_memory=bool(pin))
+        out = cls(flat, [t.shape for t in tensors])
+        for dst, src in zip(out, tensors):
+            dst.copy_(src)
+        return out
+
+    def to(self, device, non_blocking: bool = True) -> 'PackedSample':
+        device = torch.device(device)
+        if self.flat.device == device:
+            return self
+        return PackedSample(self.flat.to(device, non_blocking=non_blocking), self.shapes)
+
+    def clone(self) -> 'PackedSample':
+        return PackedSample(self.flat.clone(), self.shapes)
+
+    def same_layout(self, other) -> bool:
+        return isinstance(other, PackedSample) and other.shapes == self.shapes and other.flat.dtype == self.flat.dtype
+
+
 def move_to_device(sample, device, non_blocking: bool = True):
     """Copy every tensor of a (nested) sample to ``device``.
 
@@ -41,6 +88,8 @@ def move_to_device(sample, device, non_blocking: bool = True):
     are pinned first when they are not already, so the copy can overlap with compute.
     """
     device = torch.device(device)
+    if isinstance(sample, PackedSample):
+        return sample.to(device, non_blocking=non_blocking)
 
     def _move(t):
         if t.device == device:

@@ -196,10 +196,13 @@ def test_reference_style_checkpoint_without_extra_state_loads(tmp_path):
     assert extra is None and ctl2.get_num_updates() == 5 and itr.epoch == 0
 
 
-def test_mid_epoch_checkpoint_and_exact_resume(tmp_path):
+@pytest.mark.parametrize('prefetch', ['0', '1'])
+def test_mid_epoch_checkpoint_and_exact_resume(tmp_path, monkeypatch, prefetch):
     """--save-interval-updates works (unreachable in the reference) and a resumed run reproduces the
-    uninterrupted one bit for bit (iterator fast-forward + seed + optimizer state)."""
+    uninterrupted one bit for bit (iterator fast-forward + seed + optimizer state) -- also with the background
+    prefetcher reading ahead of the trainer (the GPU default; forced on here)."""
     from hetseq_b200 import train as train_mod
+    monkeypatch.setenv('HETSEQ_PREFETCH', prefetch)
     full_dir = tmp_path / 'full'; full_dir.mkdir()
     a, _, _ = _tiny_mnist_controller(full_dir, max_epoch=1)
     ctl_full = train_mod.main(a)

@@ -184,3 +184,80 @@ def test_mnist_dataset(tmp_path):
     torch.testing.assert_close(img[0], (raw - 0.1307) / 0.3081)
     b = ds.fetch_batch([0, 3])
     assert b[0].shape == (2, 1, 28, 28) and torch.equal(b[0][1], img)
+
+
+def test_prefetch_iterator_keeps_resume_position_exact():
+    """A prefetcher reads ahead of the trainer; the checkpointed position must be the trainer's. Also checks the
+    worker-thread transform and that resuming from the recorded position yields exactly the untrained batches."""
+    import torch
+    from hetseq_b200.data import iterators
+
+    class DS(torch.utils.data.Dataset):
+        def __len__(self):
+            return 40
+
+        def __getitem__(self, i):
+            return torch.tensor([i])
+
+        def collater(self, samples):
+            return None if len(samples) == 0 else [torch.stack(samples)]
+
+    ds = DS()
+    batches = [[2 * i, 2 * i + 1] for i in range(20)]
+
+    def make():
+        return iterators.EpochBatchIterator(ds, ds.collater, batches, seed=3, num_shards=1, shard_id=0)
+
+    ref = make()
+    expected = [b[0].flatten().tolist() for b in ref.next_epoch_itr(shuffle=True)]
+
+    ebi = make()
+    itr = iterators.GroupedIterator(ebi.next_epoch_itr(shuffle=True), 2)
+    seen_transform = []
+    pre = iterators.PrefetchIterator(itr, depth=3, pin_memory=False,
+                                     transform=lambda chunk: (seen_transform.append(len(chunk)) or chunk)).attach_to(ebi)
+    got = []
+    for k, chunk in enumerate(pre):
+        got += [b[0].flatten().tolist() for b in chunk]
+        if k == 2:
+            break
+    import time
+    time.sleep(0.2)                                  # let the worker run ahead
+    assert ebi._cur_epoch_itr.count > 6              # the reader is ahead of the trainer ...
+    state = ebi.state_dict()
+    assert state['iterations_in_epoch'] == 6         # ... but the recorded position is the trainer's
+    assert not ebi.end_of_epoch()
+    assert got == expected[:6] and seen_transform[:3] == [2, 2, 2]
+
+    resumed = make()
+    resumed.load_state_dict(state)
+    rest = [b[0].flatten().tolist() for b in resumed.next_epoch_itr(shuffle=True)]
+    assert rest == expected[6:]
+
+    # consuming everything through a prefetcher ends the epoch
+    ebi2 = make()
+    pre2 = iterators.PrefetchIterator(iterators.GroupedIterator(ebi2.next_epoch_itr(shuffle=True), 3), depth=2,
+                                      pin_memory=False).attach_to(ebi2)
+    n = sum(len(c) for c in pre2)
+    assert n == 20 and ebi2.end_of_epoch() and ebi2.iterations_in_epoch == 20
+
+
+def test_packed_sample_views_one_buffer():
+    import torch
+    from hetseq_b200.utils.utils import PackedSample, move_to_device
+    parts = [torch.arange(6, dtype=torch.int32).view(2, 3), torch.tensor([7], dtype=torch.int32),
+             torch.arange(5, dtype=torch.int32)]
+    p = PackedSample.pack(parts)
+    assert isinstance(p, list) and len(p) == 3 and all(torch.equal(a, b) for a, b in zip(p, parts))
+    assert all(t.data_ptr() % 16 == p.flat.data_ptr() % 16 for t in p)          # views stay 16-byte aligned
+    p.flat += 1                                                               # views alias the flat buffer
+    assert p[1].item() == 8
+    c = p.clone()
+    assert c.same_layout(p) and c.flat.data_ptr() != p.flat.data_ptr() and torch.equal(c[2], p[2])
+    assert move_to_device(p, 'cpu') is p
+    assert PackedSample.pack([torch.ones(2), torch.ones(2, dtype=torch.int32)]) is None     # mixed dtypes
+    assert not p.same_layout([t for t in p])
+    # the BERT task packs its 7 int32 tensors when preparing for a CUDA device
+    from hetseq_b200.data.iterators import PrefetchIterator
+    pre = PrefetchIterator(iter([[p]]), depth=1, pin_memory=False)
+    assert next(pre)[0] is p
