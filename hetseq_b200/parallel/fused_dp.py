@@ -118,7 +118,10 @@ class FusedBackend(AllReduceBackend):
         self.epoch_t = torch.zeros(1, dtype=torch.int32, device=dev)
         # reduce-scatter grid: 2 CTAs per SM measured best next to backward on 8 GPUs (14.2 ms/step vs 14.7 with
         # 148 and 15.4 with one CTA per chunk); HETSEQ_RS_BLOCKS pins another size, -1 = one CTA per owned chunk
-        rb = int(os.environ.get('HETSEQ_RS_BLOCKS', '0') or getattr(args, 'fused_rs_blocks', 0) or 296)
+        # (2 GPUs: 148 CTAs 13.85 ms vs 296 CTAs 14.24 ms -- with one peer there are few loads in flight per
+        # thread anyway and the second CTA per SM only takes slots from backward)
+        rb = int(os.environ.get('HETSEQ_RS_BLOCKS', '0') or getattr(args, 'fused_rs_blocks', 0)
+                 or (148 if W <= 2 else 296))
         self.rs_blocks = 0 if rb < 0 else rb
         torch.cuda.synchronize()
         dist.barrier(group=self.group, device_ids=[dev.index])
