@@ -1,0 +1,245 @@
+"""Runs in its own interpreter (the reference uses flat module names such as ``utils``, ``data``, ``options`` that must
+not leak into the test process): imports the UNMODIFIED reference from baseline/_ref and compares this framework
+against it, component by component, on CPU. Prints one JSON object {check: "ok" | error text}.
+
+The reference modules are used as oracles only; nothing here is timed."""
+import json
+import os
+import sys
+import traceback
+import types
+import warnings
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = os.path.join(ROOT, 'baseline', '_ref')
+warnings.filterwarnings('ignore')
+
+
+def _stub_missing():
+    for name in ('boto3', 'botocore', 'botocore.exceptions', 'h5py'):
+        try:
+            __import__(name)
+        except Exception:
+            m = types.ModuleType(name)
+            if name == 'botocore.exceptions':
+                m.ClientError = type('ClientError', (Exception,), {})
+            sys.modules[name] = m
+
+
+def check_lr_schedule():
+    import argparse
+    import lr_scheduler as ref_lr
+    from hetseq_b200.optim import lr_scheduler as my_lr
+
+    class Opt(object):
+        def __init__(self):
+            self.lr = None
+
+        def set_lr(self, lr):
+            self.lr = lr
+
+        def get_lr(self):
+            return self.lr
+
+    for warm, total, power, end, fa in ((0, 50, 1.0, 0.0, None), (10, 100, 1.0, 0.0, None), (7, 60, 2.0, 1e-5, None),
+                                        (5, 40, 0.5, 1e-6, 2)):
+        ns = dict(lr=[1e-3, 5e-4], warmup_updates=warm, total_num_update=total, power=power, end_learning_rate=end,
+                  force_anneal=fa)
+        import optim as ref_optim
+
+        class RefOpt(ref_optim._Optimizer):      # the reference insists on its own wrapper type
+            def __init__(self):
+                self.lr = None
+
+            def set_lr(self, lr):
+                self.lr = lr
+
+            def get_lr(self):
+                return self.lr
+
+        a, b = RefOpt(), Opt()
+        r = ref_lr.PolynomialDecayScheduler(argparse.Namespace(**ns), a)
+        m = my_lr.PolynomialDecayScheduler(argparse.Namespace(**ns), b)
+        assert abs(a.get_lr() - b.get_lr()) < 1e-15, ('init', a.get_lr(), b.get_lr())
+        for epoch in range(1, 4):
+            r.step(epoch)
+            m.step(epoch)
+            for n in range((epoch - 1) * 30, epoch * 30):
+                x, y = r.step_update(n), m.step_update(n)
+                assert abs(x - y) <= 1e-12 * max(1.0, abs(x)), (ns, epoch, n, x, y)
+
+
+def check_optimizers():
+    import torch
+    import optim as ref_optim
+    from hetseq_b200.optim import tensor_optimizers as mine
+    torch.manual_seed(0)
+    shapes = [(7, 5), (13,), (3, 4, 2)]
+    for kind in ('adam', 'adadelta'):
+        p_ref = [torch.nn.Parameter(torch.randn(s)) for s in shapes]
+        p_my = [torch.nn.Parameter(p.detach().clone()) for p in p_ref]
+        if kind == 'adam':
+            o_ref = ref_optim.Adam(p_ref, lr=1e-2, betas=(0.9, 0.98), eps=1e-6, weight_decay=0.01)
+            o_my = mine.Adam(p_my, lr=1e-2, betas=(0.9, 0.98), eps=1e-6, weight_decay=0.01)
+        else:
+            o_ref = ref_optim.Adadelta(p_ref, lr=1.0, rho=0.9, eps=1e-6, weight_decay=0.01)
+            o_my = mine.Adadelta(p_my, lr=1.0, rho=0.9, eps=1e-6, weight_decay=0.01)
+        for step in range(6):
+            for a, b in zip(p_ref, p_my):
+                g = torch.randn_like(a)
+                a.grad, b.grad = g.clone(), g.clone()
+            o_ref.step()
+            o_my.step()
+            for a, b in zip(p_ref, p_my):
+                assert torch.allclose(a, b, rtol=1e-6, atol=1e-7), (kind, step, (a - b).abs().max().item())
+
+
+def check_iterators():
+    import data.iterators as ref_it
+    from hetseq_b200.data import iterators as my_it
+    items = list(range(23))
+    for shards in (1, 2, 3, 8):
+        for sid in range(shards):
+            a = list(ref_it.ShardedIterator(items, shards, sid, fill_value=[]))
+            b = list(my_it.ShardedIterator(items, shards, sid, fill_value=[]))
+            assert a == b, (shards, sid, a, b)
+    for chunk in (1, 2, 4, 5):
+        a = list(ref_it.GroupedIterator(ref_it.CountingIterator(items), chunk))
+        b = list(my_it.GroupedIterator(my_it.CountingIterator(items), chunk))
+        assert a == b, (chunk, a, b)
+    a, b = ref_it.CountingIterator(items, start=3), my_it.CountingIterator(items, start=3)
+    for _ in range(5):
+        assert next(a) == next(b)
+    assert a.count == b.count and a.has_next() == b.has_next()
+    assert list(a.skip(4)) == list(b.skip(4)) and a.count == b.count
+
+
+def check_batch_by_size():
+    import numpy as np
+    from data import data_utils as ref_du
+    from hetseq_b200.data import data_utils as my_du
+    rng = np.random.RandomState(0)
+    for trial in range(12):
+        n = int(rng.randint(1, 300))
+        sizes = rng.randint(1, 64, size=n).astype(np.int64)
+        idx = rng.permutation(n).astype(np.int64)
+        max_tokens = int(rng.choice([64, 128, 500, 4096]))
+        max_sent = int(rng.choice([1, 3, 8, 32, 1000]))
+        mult = int(rng.choice([1, 2, 8]))
+        ref = ref_du.batch_by_size(idx, lambda i: int(sizes[i]), max_tokens=max_tokens, max_sentences=max_sent,
+                                   required_batch_size_multiple=mult)
+        got = my_du.batch_by_size(idx, lambda i: int(sizes[i]), max_tokens=max_tokens, max_sentences=max_sent,
+                                  required_batch_size_multiple=mult)
+        ref = [list(map(int, b)) for b in ref]
+        got = [list(map(int, b)) for b in got]
+        assert ref == got, (trial, n, max_tokens, max_sent, mult)
+
+
+def check_bert_loss_and_grads():
+    """Same weights, same batch, fp32 on CPU: the reference's BertForPreTraining against this framework's PyTorch
+    path (all positions through the MLM head, as in the reference, and the gathered-rows default)."""
+    import torch
+    import bert_modeling as ref_bm
+    from hetseq_b200.models import bert as my_bm
+    cfg = dict(vocab_size=120, hidden_size=64, num_hidden_layers=2, num_attention_heads=4, intermediate_size=128,
+               hidden_act='gelu', hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0,
+               max_position_embeddings=32, type_vocab_size=2, initializer_range=0.02)
+    torch.manual_seed(0)
+    ref = ref_bm.BertForPreTraining(ref_bm.BertConfig.from_dict(cfg)).float()
+    mine = my_bm.BertForPreTraining(my_bm.BertConfig.from_dict(cfg)).float()
+    assert list(ref.state_dict().keys()) == list(mine.state_dict().keys()), 'state-dict key order/names differ'
+    assert sum(p.numel() for p in ref.parameters()) == sum(p.numel() for p in mine.parameters())
+    mine.load_state_dict(ref.state_dict())
+    B, S = 4, 16
+    g = torch.Generator().manual_seed(1)
+    ids = torch.randint(0, 120, (B, S), generator=g)
+    seg = torch.randint(0, 2, (B, S), generator=g)
+    mask = torch.ones(B, S, dtype=torch.long)
+    mask[1, 11:] = 0
+    labels = torch.full((B, S), -1, dtype=torch.long)
+    labels[0, 3], labels[0, 9], labels[2, 5], labels[3, 1] = 7, 11, 13, 17
+    nsp = torch.tensor([0, 1, 1, 0])
+    ref.train()
+    mine.train()
+    lr = ref(ids, seg, mask, labels, nsp)
+    lm = mine(ids, seg, mask, labels, nsp)
+    assert abs(lr.item() - lm.item()) < 1e-5, (lr.item(), lm.item())
+    lr.backward()
+    lm.backward()
+    gr = dict(ref.named_parameters())
+    for name, p in mine.named_parameters():
+        a, b = gr[name].grad, p.grad
+        assert a is not None and b is not None, name
+        assert torch.allclose(a, b, rtol=1e-4, atol=1e-6), (name, (a - b).abs().max().item())
+    mine.mlm_all_positions = True
+    mine.zero_grad()
+    lm2 = mine(ids, seg, mask, labels, nsp)
+    assert abs(lr.item() - lm2.item()) < 1e-5
+
+
+def check_meters_and_format():
+    import meters as ref_m
+    import progress_bar as ref_pb
+    from hetseq_b200.utils import meters as my_m, progress_bar as my_pb
+    a, b = ref_m.AverageMeter(), my_m.AverageMeter()
+    for v, n in ((1.5, 2), (3.0, 1), (0.25, 5)):
+        a.update(v, n)
+        b.update(v, n)
+    assert (a.val, a.sum, a.count, a.avg) == (b.val, b.sum, b.count, b.avg)
+    assert ref_pb.format_stat(a) == my_pb.format_stat(b)
+    for x in (3, 0.000123456, 12345.678):
+        assert ref_pb.format_stat(x) == my_pb.format_stat(x)
+
+
+def check_flag_defaults():
+    """Every flag of the reference's training parser exists here with the same default."""
+    import options as ref_opt
+    from hetseq_b200 import options as my_opt
+    for task, opt in (('bert', 'adam'), ('mnist', 'adadelta')):
+        rp = ref_opt.get_training_parser(task=task, optimizer=opt, lr_scheduler='PolynomialDecayScheduler')
+        mp = my_opt.get_training_parser(task=task, optimizer=opt)
+        mine = {}
+        for act in mp._actions:
+            for s in act.option_strings:
+                mine[s] = act
+        skip = {'--distributed-world-size'}       # default = number of visible GPUs in both; environment dependent
+        for act in rp._actions:
+            for s in act.option_strings:
+                if s in ('-h', '--help') or s in skip:
+                    continue
+                assert s in mine, 'reference flag {} missing'.format(s)
+                rd, md = act.default, mine[s].default
+                if s in ('--distributed-backend',):
+                    continue                      # nccl there; nccl-or-gloo by device here
+                same = rd == md or str(rd) == str(md)
+                if not same:
+                    try:
+                        same = float(rd) == float(md)
+                    except (TypeError, ValueError):
+                        pass
+                assert same, (s, rd, md)
+
+
+CHECKS = [check_lr_schedule, check_optimizers, check_iterators, check_batch_by_size, check_bert_loss_and_grads,
+          check_meters_and_format, check_flag_defaults]
+
+
+def main():
+    out = {}
+    if not os.path.exists(os.path.join(REF, 'controller.py')):
+        print(json.dumps({'unavailable': 'baseline/_ref not installed'}))
+        return
+    _stub_missing()
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, REF)
+    for fn in CHECKS:
+        try:
+            fn()
+            out[fn.__name__] = 'ok'
+        except BaseException:
+            out[fn.__name__] = traceback.format_exc()[-1500:]
+    print('RESULT ' + json.dumps(out))
+
+
+if __name__ == '__main__':
+    main()
