@@ -220,7 +220,86 @@ def check_flag_defaults():
                 assert same, (s, rd, md)
 
 
-CHECKS = [check_lr_schedule, check_optimizers, check_iterators, check_batch_by_size, check_bert_loss_and_grads,
+def check_checkpoint_interchange():
+    """Files written by the reference's save_state load into this framework's Controller (weights, Adam state in
+    the per-parameter layout, update counter, LR-scheduler state); files written here feed the reference's own
+    optimizer wrapper. MNIST net on CPU."""
+    import argparse
+    import tempfile
+    import torch
+    import checkpoint_utils as ref_ck
+    import lr_scheduler as ref_lr
+    import optim as ref_optim
+    import tasks as ref_tasks
+    from hetseq_b200 import options, registry
+    from hetseq_b200.controller import Controller
+    from hetseq_b200.data.mnist_dataset import make_synthetic_mnist
+
+    tmp = tempfile.mkdtemp(prefix='hsparity')
+    data = os.path.join(tmp, 'data')
+    make_synthetic_mnist(data, 32, 16)
+    argv = ['--data', data, '--cpu', '--max-sentences', '16', '--lr', '0.01', '--save-dir', os.path.join(tmp, 'ckpt'),
+            '--distributed-world-size', '1', '--log-format', 'none', '--adam-betas', '(0.9, 0.98)', '--adam-eps', '1e-6',
+            '--weight-decay', '0.01']
+    a = options.make_args('mnist', 'adam', argv=argv)
+    task = registry.lookup('task', 'mnist').setup_task(a)
+    ctl = Controller(a, task, task.build_model(a))
+
+    # ---- reference side: its MNISTNet, its _Adam wrapper, two updates, its save_state
+    torch.manual_seed(5)
+    ref_model = ref_tasks.MNISTNet()
+    assert list(ref_model.state_dict().keys()) == list(ctl.get_model().state_dict().keys())
+    rargs = argparse.Namespace(lr=[0.01], adam_betas='(0.9, 0.98)', adam_eps=1e-6, weight_decay=0.01, warmup_updates=0,
+                               total_num_update=100, power=1.0, end_learning_rate=0.0, force_anneal=None,
+                               no_save_optimizer_state=False)
+    ref_opt = ref_optim._Adam(rargs, list(ref_model.parameters()))
+    ref_sched = ref_lr.PolynomialDecayScheduler(rargs, ref_opt)
+    for _ in range(2):
+        for p in ref_model.parameters():
+            p.grad = torch.randn_like(p) * 0.1
+        ref_opt.step()
+    f1 = os.path.join(tmp, 'from_reference.pt')
+    ref_ck.save_state(f1, rargs, ref_model.state_dict(), None, ref_opt, ref_sched, 2)
+    # ---- this framework reads it
+    ctl.load_checkpoint(f1)
+    assert ctl.get_num_updates() == 2
+    for (k, v), (_, w) in zip(ref_model.state_dict().items(), ctl.get_model().state_dict().items()):
+        assert torch.equal(v, w), k
+    mine_state = ctl.optimizer.state_dict()
+    ref_state = ref_opt.state_dict()
+    assert set(mine_state['state'].keys()) == set(ref_state['state'].keys())
+    for idx, st in ref_state['state'].items():
+        for key in ('exp_avg', 'exp_avg_sq'):
+            assert torch.allclose(st[key].float(), mine_state['state'][idx][key].float(), rtol=0, atol=0), (idx, key)
+        assert int(st['step']) == int(mine_state['state'][idx]['step'])
+    # one more identical update on both sides keeps them in lock-step (same Adam math on the restored state)
+    grads = [torch.randn_like(p) * 0.1 for p in ref_model.parameters()]
+    for p, g in zip(ref_model.parameters(), grads):
+        p.grad = g.clone()
+    ref_opt.step()
+    ctl.zero_grad()
+    for p, g in zip(ctl.get_model().parameters(), grads):
+        p.grad = g.clone() if p.grad is None else p.grad.copy_(g)
+    ctl.optimizer.step()
+    for (k, v), (_, w) in zip(ref_model.state_dict().items(), ctl.get_model().state_dict().items()):
+        assert torch.allclose(v, w, rtol=1e-6, atol=1e-7), (k, (v - w).abs().max().item())
+    # ---- and back: a file written here feeds the reference's optimizer wrapper
+    f2 = os.path.join(tmp, 'from_here.pt')
+    ctl.save_checkpoint(f2, {'train_iterator': {'epoch': 1, 'iterations_in_epoch': 0}})
+    state = torch.load(f2, map_location='cpu', weights_only=False)    # (the reference's own loader predates weights_only)
+    assert set(state) >= {'args', 'model', 'optimizer_history', 'extra_state', 'last_optimizer_state'}
+    assert state['optimizer_history'][-1]['optimizer_name'] == '_Adam'
+    ref_model2 = ref_tasks.MNISTNet()
+    ref_model2.load_state_dict(state['model'])
+    ref_opt2 = ref_optim._Adam(rargs, list(ref_model2.parameters()))
+    ref_opt2.load_state_dict(state['last_optimizer_state'])
+    st2 = ref_opt2.state_dict()['state']
+    for idx, st in ref_opt.state_dict()['state'].items():
+        assert torch.allclose(st['exp_avg'], st2[idx]['exp_avg'], rtol=1e-6, atol=1e-8), idx
+        assert int(st2[idx]['step']) == 3
+
+
+CHECKS = [check_checkpoint_interchange, check_lr_schedule, check_optimizers, check_iterators, check_batch_by_size, check_bert_loss_and_grads,
           check_meters_and_format, check_flag_defaults]
 
 

@@ -1,6 +1,6 @@
 """This framework against the UNMODIFIED reference (baseline/_ref) used as an oracle, component by component, on
 CPU: LR schedule, Adam / Adadelta math, iterators, the batch planner vs the reference's Cython extension, the BERT
-pre-training loss and every parameter gradient, meters / log formatting, flag names and defaults.
+pre-training loss and every parameter gradient, checkpoint files in both directions, meters / log formatting, flag names and defaults.
 
 The checks run in a separate interpreter (tests/ref_parity_worker.py) because the reference uses flat module names
 (``utils``, ``data``, ``options`` ...). Skipped when the reference is not installed (baseline/install_reference.sh)."""
@@ -12,7 +12,7 @@ import sys
 import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-CHECKS = ['check_lr_schedule', 'check_optimizers', 'check_iterators', 'check_batch_by_size',
+CHECKS = ['check_checkpoint_interchange', 'check_lr_schedule', 'check_optimizers', 'check_iterators', 'check_batch_by_size',
           'check_bert_loss_and_grads', 'check_meters_and_format', 'check_flag_defaults']
 _cache = {}
 
