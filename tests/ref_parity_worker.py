@@ -299,7 +299,58 @@ def check_checkpoint_interchange():
         assert int(st2[idx]['step']) == 3
 
 
-CHECKS = [check_checkpoint_interchange, check_lr_schedule, check_optimizers, check_iterators, check_batch_by_size, check_bert_loss_and_grads,
+def check_mnist_training_curve():
+    """Whole trainer against whole trainer: the reference's Controller.train_step and this framework's, same
+    initial weights, same synthetic MNIST files, 8 updates on CPU. Identical batch order (seeded shuffle), identical
+    dropout masks (seed + num_updates), identical Adadelta + clipping => the same loss curve. The reference's
+    single-process path logs the raw loss, this framework logs base 2 like the reference's fast-stat-sync path."""
+    import math
+    import tempfile
+    import torch
+    import options as ro
+    import tasks as rt
+    from controller import Controller as RefController
+    from hetseq_b200 import options, registry
+    from hetseq_b200.controller import Controller
+    from hetseq_b200.data.mnist_dataset import make_synthetic_mnist
+    tmp = tempfile.mkdtemp(prefix='hscurve')
+    data = os.path.join(tmp, 'data')
+    make_synthetic_mnist(data, 128, 16)
+    parser = ro.get_training_parser(task='mnist', optimizer='adadelta', lr_scheduler='PolynomialDecayScheduler')
+    args = ro.parse_args_and_arch(parser, ['--task', 'mnist', '--optimizer', 'adadelta', '--data', data, '--cpu',
+                                           '--max-sentences', '16', '--lr', '0.5', '--save-dir', tmp + '/ck',
+                                           '--distributed-world-size', '1', '--no-save', '--clip-norm', '25'])
+    torch.manual_seed(args.seed)
+    task = rt.MNISTTask.setup_task(args)
+    task.load_dataset('train')
+    model = task.build_model(args)
+    init = {k: v.clone() for k, v in model.state_dict().items()}
+    ctl = RefController(args, task, model)
+    ref_losses = []
+    for sample in ctl.get_train_iterator(epoch=0).next_epoch_itr(shuffle=True):
+        ref_losses.append(float(ctl.train_step([sample])['loss']))
+    a = options.make_args('mnist', 'adadelta', argv=['--data', data, '--cpu', '--max-sentences', '16', '--lr', '0.5',
+                                                    '--save-dir', tmp + '/ck2', '--distributed-world-size', '1',
+                                                    '--log-format', 'none', '--no-save', '--sample-size-mode',
+                                                    'reference', '--clip-norm', '25'])
+    torch.manual_seed(a.seed)
+    t2 = registry.lookup('task', 'mnist').setup_task(a)
+    t2.load_dataset('train')
+    m2 = t2.build_model(a)
+    m2.load_state_dict(init)
+    c2 = Controller(a, t2, m2)
+    mine = []
+    for sample in c2.get_train_iterator(epoch=0).next_epoch_itr(shuffle=True):
+        mine.append(float(c2.train_step([sample])['loss']) * math.log(2))
+    assert len(mine) == len(ref_losses) == 8
+    assert ref_losses[-1] < ref_losses[0] - 0.5, ref_losses          # it does learn
+    for i, (x, y) in enumerate(zip(ref_losses, mine)):
+        assert abs(x - y) <= 2e-5 * max(1.0, abs(x)), (i, x, y)
+    for (k, v), (_, w) in zip(model.state_dict().items(), m2.state_dict().items()):
+        assert torch.allclose(v, w, rtol=1e-4, atol=1e-6), (k, (v - w).abs().max().item())
+
+
+CHECKS = [check_mnist_training_curve, check_checkpoint_interchange, check_lr_schedule, check_optimizers, check_iterators, check_batch_by_size, check_bert_loss_and_grads,
           check_meters_and_format, check_flag_defaults]
 
 
