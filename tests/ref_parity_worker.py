@@ -350,7 +350,63 @@ def check_mnist_training_curve():
         assert torch.allclose(v, w, rtol=1e-4, atol=1e-6), (k, (v - w).abs().max().item())
 
 
-CHECKS = [check_mnist_training_curve, check_checkpoint_interchange, check_lr_schedule, check_optimizers, check_iterators, check_batch_by_size, check_bert_loss_and_grads,
+def check_bert_training_curve():
+    """BERT pre-training, whole trainer against whole trainer on CPU (fp32, dropout off): the reference's
+    LanguageModelingTask + Controller (DDP-free single process) + its Adam, and this framework with
+    --sample-size-mode reference. Same weights, same synthetic batches, 6 updates with warm-up + polynomial decay
+    + clipping + weight decay: same losses, same weights afterwards."""
+    import json as _json
+    import math
+    import tempfile
+    import torch
+    import options as ro
+    import tasks as rt
+    from controller import Controller as RefController
+    from hetseq_b200 import options, registry
+    from hetseq_b200.controller import Controller
+    from hetseq_b200.data.bert_dataset import SyntheticBertData
+    tmp = tempfile.mkdtemp(prefix='hsbertcurve')
+    cfg = dict(vocab_size=300, hidden_size=64, num_hidden_layers=2, num_attention_heads=4, intermediate_size=128,
+               hidden_act='gelu', hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0,
+               max_position_embeddings=32, type_vocab_size=2, initializer_range=0.02)
+    cfg_path = os.path.join(tmp, 'bert_config.json')
+    with open(cfg_path, 'w') as f:
+        _json.dump(cfg, f)
+    vocab = os.path.join(tmp, 'vocab.txt')
+    with open(vocab, 'w') as f:
+        f.write('\n'.join('tok%d' % i for i in range(16)))
+    ds = SyntheticBertData(6 * 4, 32, 5, 300, seed=11)
+    batches = [ds.fetch_rows(list(range(i * 4, i * 4 + 4))) for i in range(6)]
+    common = ['--config_file', cfg_path, '--max-sentences', '4', '--lr', '1e-3', '--warmup-updates', '2',
+              '--total-num-update', '20', '--weight-decay', '0.01', '--clip-norm', '1.0', '--adam-betas', '(0.9, 0.98)',
+              '--adam-eps', '1e-6', '--no-save', '--distributed-world-size', '1', '--cpu']
+    parser = ro.get_training_parser(task='bert', optimizer='adam', lr_scheduler='PolynomialDecayScheduler')
+    args = ro.parse_args_and_arch(parser, ['--task', 'bert', '--data', tmp, '--dict', vocab, '--save-dir', tmp + '/ck'] + common)
+    torch.manual_seed(args.seed)
+    task = rt.LanguageModelingTask.setup_task(args)
+    model = task.build_model(args)
+    init = {k: v.clone() for k, v in model.state_dict().items()}
+    ctl = RefController(args, task, model)
+    ref_losses = [float(ctl.train_step([[t.clone() for t in b]])['loss']) for b in batches]
+
+    a = options.make_args('bert', 'adam', argv=['--synthetic-data', '--save-dir', tmp + '/ck2', '--log-format', 'none',
+                                                '--sample-size-mode', 'reference'] + common)
+    torch.manual_seed(a.seed)
+    t2 = registry.lookup('task', 'bert').setup_task(a)
+    m2 = t2.build_model(a)
+    m2.load_state_dict(init)
+    c2 = Controller(a, t2, m2)
+    # logged here: sum / (sample_size * ln 2) like the reference's fast-stat-sync path, and in reference mode
+    # sample_size is the sequence length (32); the reference's single-process path logs the raw loss
+    mine = [float(c2.train_step([[t.clone() for t in b]])['loss']) * math.log(2) * 32 for b in batches]
+    for i, (x, y) in enumerate(zip(ref_losses, mine)):
+        assert abs(x - y) <= 5e-5 * max(1.0, abs(x)), (i, ref_losses, mine)
+    assert abs(ctl.get_lr() - c2.get_lr()) < 1e-12, (ctl.get_lr(), c2.get_lr())
+    worst = max((v - w).abs().max().item() for (k, v), (_, w) in zip(model.state_dict().items(), m2.state_dict().items()))
+    assert worst < 2e-5, worst
+
+
+CHECKS = [check_bert_training_curve, check_mnist_training_curve, check_checkpoint_interchange, check_lr_schedule, check_optimizers, check_iterators, check_batch_by_size, check_bert_loss_and_grads,
           check_meters_and_format, check_flag_defaults]
 
 

@@ -12,7 +12,7 @@ import sys
 import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-CHECKS = ['check_mnist_training_curve', 'check_checkpoint_interchange', 'check_lr_schedule', 'check_optimizers', 'check_iterators', 'check_batch_by_size',
+CHECKS = ['check_bert_training_curve', 'check_mnist_training_curve', 'check_checkpoint_interchange', 'check_lr_schedule', 'check_optimizers', 'check_iterators', 'check_batch_by_size',
           'check_bert_loss_and_grads', 'check_meters_and_format', 'check_flag_defaults']
 _cache = {}
 
