@@ -1,26 +1,72 @@
-"""Learning-rate schedules (reference: lr_scheduler.py:1-105).
+"""Learning-rate schedules (behaviour of the reference's lr_scheduler.py:1-105, checked against it update by update in
+tests/test_reference_parity.py).
 
-``PolynomialDecayScheduler``: linear warm-up over ``--warmup-updates`` then polynomial decay to
-``--end-learning-rate`` at ``--total-num-update``; ``step(epoch)`` switches to the epoch-indexed
-``--lr`` list unless ``--force-anneal`` has been reached.
+Design: a schedule is a pure function ``lr(base_lr, num_updates) -> float`` (``polynomial_lr`` / ``warmup_constant_lr``)
+plus a small amount of epoch state (which entry of the per-epoch ``--lr`` list is the base). The classes below only
+hold that state, push the value into the optimizer (from where it reaches the fused update kernels through a
+device scalar, so a schedule never forces a CUDA-graph re-capture) and carry ``best`` for checkpoints.
+
+Observable contract kept from the reference:
+* the constructor sets ``lr = lr[0] / warmup_updates`` when there is a warm-up (else ``lr[0]``);
+* ``step(epoch)`` selects ``lr[min(epoch, len - 1)]`` unless ``--force-anneal`` has been reached, re-applies the LAST
+  warm-up factor and returns the learning rate; it also tracks the best validation loss;
+* ``step_update(n)``: linear warm-up while ``n <= warmup``, ``--end-learning-rate`` from ``--total-num-update`` on,
+  otherwise ``(lr - end) * (1 - (n - warmup) / (total - warmup)) ** power + end``;
+* ``state_dict() == {'best': ...}``.
 """
 from __future__ import annotations
+
+from typing import Optional, Sequence
 
 from hetseq_b200.registry import register_lr_scheduler
 
 
+# ---- pure schedule math -------------------------------------------------------------------------------
+def warmup_fraction(num_updates: int, warmup: int) -> Optional[float]:
+    """Fraction of the base LR during linear warm-up, or None once warm-up is over (or absent)."""
+    if warmup > 0 and num_updates <= warmup:
+        return num_updates / float(warmup)
+    return None
+
+
+def polynomial_lr(base_lr: float, num_updates: int, warmup: int, total: int, end_lr: float, power: float) -> float:
+    frac = warmup_fraction(num_updates, warmup)
+    if frac is not None:
+        return frac * base_lr
+    if num_updates >= total:
+        return end_lr
+    remaining = 1 - (num_updates - warmup) / (total - warmup)
+    return (base_lr - end_lr) * remaining ** power + end_lr
+
+
+def epoch_base_lr(lrs: Sequence[float], epoch: int, force_anneal: Optional[int], current: float) -> float:
+    """Entry of the per-epoch ``--lr`` list for ``epoch``; frozen at ``current`` once force-anneal is reached."""
+    if force_anneal is not None and epoch >= force_anneal:
+        return current
+    return lrs[min(epoch, len(lrs) - 1)]
+
+
+# ---- stateful wrappers ----------------------------------------------------------------------------------
 class _LRScheduler(object):
+    """Holds the optimizer, the best validation loss seen, and the checkpointable state."""
+
     def __init__(self, args, optimizer):
-        super().__init__()
-        if not hasattr(optimizer, 'set_lr') or not hasattr(optimizer, 'get_lr'):
-            raise ValueError('optimizer must expose get_lr()/set_lr() (an hetseq_b200.optim._Optimizer)')
-        self.args = args
-        self.optimizer = optimizer
-        self.best = None
+        for needed in ('set_lr', 'get_lr'):
+            if not hasattr(optimizer, needed):
+                raise ValueError('optimizer must expose get_lr()/set_lr() (an hetseq_b200.optim._Optimizer)')
+        self.args, self.optimizer, self.best = args, optimizer, None
 
     @staticmethod
     def add_args(parser):
         pass
+
+    def _apply(self, lr: float) -> float:
+        self.optimizer.set_lr(lr)
+        return self.optimizer.get_lr()
+
+    def _track_best(self, val_loss) -> None:
+        if val_loss is not None:
+            self.best = val_loss if self.best is None else min(self.best, val_loss)
 
     def state_dict(self):
         return {'best': self.best}
@@ -29,16 +75,22 @@ class _LRScheduler(object):
         self.best = state_dict['best']
 
     def step(self, epoch, val_loss=None):
-        """Update the learning rate at the end of the given epoch."""
-        if val_loss is not None:
-            if self.best is None:
-                self.best = val_loss
-            else:
-                self.best = min(self.best, val_loss)
+        """End of an epoch."""
+        self._track_best(val_loss)
 
     def step_update(self, num_updates):
-        """Update the learning rate after each update."""
+        """After every optimizer update."""
         return self.optimizer.get_lr()
+
+
+def _common_args(parser, polynomial: bool) -> None:
+    parser.add_argument('--force-anneal', '--fa', type=int, metavar='N', help='force annealing at specified epoch')
+    parser.add_argument('--warmup-updates', default=0, type=int, metavar='N',
+                        help='warmup the learning rate linearly for the first N updates')
+    if polynomial:
+        parser.add_argument('--end-learning-rate', default=0.0, type=float)
+        parser.add_argument('--power', default=1.0, type=float)
+        parser.add_argument('--total-num-update', default=1000000, type=int)
 
 
 @register_lr_scheduler('PolynomialDecayScheduler')
@@ -46,72 +98,55 @@ class PolynomialDecayScheduler(_LRScheduler):
     def __init__(self, args, optimizer):
         super().__init__(args, optimizer)
         args.warmup_updates = getattr(args, 'warmup_updates', 0) or 0
-        self.lr = args.lr[0]
-        self.warmup_factor = 1. / args.warmup_updates if args.warmup_updates > 0 else 1
-        self.end_learning_rate = args.end_learning_rate
-        self.total_num_update = args.total_num_update
-        self.power = args.power
-        self.optimizer.set_lr(self.warmup_factor * self.lr)
+        self.warmup = args.warmup_updates
+        self.lr = args.lr[0]                              # base LR of the current epoch
+        self.end_learning_rate, self.total_num_update, self.power = \
+            args.end_learning_rate, args.total_num_update, args.power
+        # factor applied by step(): 1/warmup before the first update, then the last warm-up fraction
+        self.warmup_factor = 1. / self.warmup if self.warmup > 0 else 1
+        self._apply(self.warmup_factor * self.lr)
 
     @staticmethod
     def add_args(parser):
-        parser.add_argument('--force-anneal', '--fa', type=int, metavar='N',
-                            help='force annealing at specified epoch')
-        parser.add_argument('--warmup-updates', default=0, type=int, metavar='N',
-                            help='warmup the learning rate linearly for the first N updates')
-        parser.add_argument('--end-learning-rate', default=0.0, type=float)
-        parser.add_argument('--power', default=1.0, type=float)
-        parser.add_argument('--total-num-update', default=1000000, type=int)
+        _common_args(parser, polynomial=True)
 
     def get_next_lr(self, epoch):
-        lrs = self.args.lr
-        if self.args.force_anneal is None or epoch < self.args.force_anneal:
-            return lrs[min(epoch, len(lrs) - 1)]
-        return self.optimizer.get_lr()
+        return epoch_base_lr(self.args.lr, epoch, self.args.force_anneal, self.optimizer.get_lr())
 
     def step(self, epoch, val_loss=None):
-        super().step(epoch, val_loss)
+        self._track_best(val_loss)
         self.lr = self.get_next_lr(epoch)
-        self.optimizer.set_lr(self.warmup_factor * self.lr)
-        return self.optimizer.get_lr()
+        return self._apply(self.warmup_factor * self.lr)
 
     def step_update(self, num_updates):
-        warmup = self.args.warmup_updates
-        if warmup > 0 and num_updates <= warmup:
-            self.warmup_factor = num_updates / float(warmup)
-            lr = self.warmup_factor * self.lr
-        elif num_updates >= self.total_num_update:
-            lr = self.end_learning_rate
-        else:
-            lr_range = self.lr - self.end_learning_rate
-            pct_remaining = 1 - (num_updates - warmup) / (self.total_num_update - warmup)
-            lr = lr_range * pct_remaining ** self.power + self.end_learning_rate
-        self.optimizer.set_lr(lr)
-        return self.optimizer.get_lr()
+        frac = warmup_fraction(num_updates, self.warmup)
+        if frac is not None:
+            self.warmup_factor = frac
+        return self._apply(polynomial_lr(self.lr, num_updates, self.warmup, self.total_num_update,
+                                         self.end_learning_rate, self.power))
 
 
 @register_lr_scheduler('fixed')
 class FixedScheduler(_LRScheduler):
-    """Constant epoch-indexed LR with optional linear warm-up (handy for tests and MNIST)."""
+    """Constant epoch-indexed LR with optional linear warm-up (handy for tests and MNIST); not in the reference."""
 
     def __init__(self, args, optimizer):
         super().__init__(args, optimizer)
         self.lr = args.lr[0]
         self.warmup = getattr(args, 'warmup_updates', 0) or 0
-        self.optimizer.set_lr(self.lr if self.warmup == 0 else self.lr / self.warmup)
+        self._apply(self.lr if self.warmup == 0 else self.lr / self.warmup)
 
     @staticmethod
     def add_args(parser):
-        parser.add_argument('--force-anneal', '--fa', type=int, metavar='N')
-        parser.add_argument('--warmup-updates', default=0, type=int, metavar='N')
+        _common_args(parser, polynomial=False)
 
     def step(self, epoch, val_loss=None):
-        super().step(epoch, val_loss)
+        self._track_best(val_loss)
         self.lr = self.args.lr[min(epoch, len(self.args.lr) - 1)]
-        self.optimizer.set_lr(self.lr)
-        return self.optimizer.get_lr()
+        return self._apply(self.lr)
 
     def step_update(self, num_updates):
-        if self.warmup > 0 and num_updates <= self.warmup:
-            self.optimizer.set_lr(self.lr * num_updates / float(self.warmup))
+        frac = warmup_fraction(num_updates, self.warmup)
+        if frac is not None:
+            self.optimizer.set_lr(self.lr * frac)
         return self.optimizer.get_lr()
