@@ -13,68 +13,55 @@ from typing import List, Optional
 
 
 class AverageMeter(object):
-    """Computes and stores the average and current value."""
+    """Running weighted mean; ``val`` is the last value (attributes val / avg / sum / count as in the reference)."""
 
     def __init__(self):
-        self.reset()
+        self.val = self.avg = self.sum = self.count = 0
 
-    def reset(self):
-        self.val = 0
-        self.avg = 0
-        self.sum = 0
-        self.count = 0
+    reset = __init__
 
     def update(self, val, n=1):
-        self.val = val
-        self.sum += val * n
-        self.count += n
+        self.val, self.sum, self.count = val, self.sum + val * n, self.count + n
         self.avg = self.sum / self.count if self.count else 0
 
 
 class TimeMeter(object):
-    """Average occurrence of some event per second (wall clock since ``reset``)."""
+    """Events per second of host wall clock since ``reset`` (attributes init / start / n)."""
 
     def __init__(self, init=0):
-        self.reset(init)
+        self.init, self.start, self.n = init, time.time(), 0
 
-    def reset(self, init=0):
-        self.init = init
-        self.start = time.time()
-        self.n = 0
+    reset = __init__
 
     def update(self, val=1):
         self.n += val
 
     @property
-    def avg(self):
-        elapsed = self.elapsed_time
-        return self.n / elapsed if elapsed > 0 else 0.0
-
-    @property
     def elapsed_time(self):
         return self.init + (time.time() - self.start)
 
+    @property
+    def avg(self):
+        t = self.elapsed_time
+        return self.n / t if t > 0 else 0.0
+
 
 class StopwatchMeter(object):
-    """Sum / average duration of some event in seconds."""
+    """Accumulated host seconds between ``start()`` and ``stop()`` (attributes sum / n / start_time)."""
 
     def __init__(self):
-        self.reset()
+        self.sum, self.n, self.start_time = 0, 0, None
+
+    reset = __init__
 
     def start(self):
         self.start_time = time.time()
 
     def stop(self, n=1):
-        if self.start_time is not None:
-            delta = time.time() - self.start_time
-            self.sum += delta
+        began, self.start_time = self.start_time, None
+        if began is not None:
+            self.sum += time.time() - began
             self.n += n
-            self.start_time = None
-
-    def reset(self):
-        self.sum = 0
-        self.n = 0
-        self.start_time = None
 
     @property
     def avg(self):
