@@ -17,7 +17,6 @@ Fixes relative to the reference:
 """
 from __future__ import annotations
 
-import collections
 import logging
 import os
 import re
@@ -30,93 +29,96 @@ import torch
 from hetseq_b200.options import literal
 
 
+EPOCH_PATTERN = r'checkpoint(\d+)\.pt'
+UPDATES_PATTERN = r'checkpoint_\d+_(\d+)\.pt'
+
+
+def planned_files(args, epoch: int, updates: int, end_of_epoch: bool, val_loss, best) -> list:
+    """File names one call to ``save_checkpoint`` writes, first = the one actually serialised (the others are
+    copies of it): end-of-epoch file every ``--save-interval`` epochs, mid-epoch file every
+    ``--save-interval-updates`` updates, ``checkpoint_best.pt`` when the validation loss ties or improves on the
+    best so far (direction per ``--maximize-best-checkpoint-metric``), ``checkpoint_last.pt`` always -- each unless
+    its ``--no-*`` flag says otherwise."""
+    names = []
+    if end_of_epoch:
+        if not args.no_epoch_checkpoints and epoch % args.save_interval == 0:
+            names.append('checkpoint{}.pt'.format(epoch))
+    elif args.save_interval_updates > 0 and updates % args.save_interval_updates == 0:
+        names.append('checkpoint_{}_{}.pt'.format(epoch, updates))
+    if val_loss is not None:
+        improved = best is None or (val_loss >= best if args.maximize_best_checkpoint_metric else val_loss <= best)
+        if improved:
+            names.append('checkpoint_best.pt')
+    if not args.no_last_checkpoints:
+        names.append('checkpoint_last.pt')
+    return names
+
+
+def prune(save_dir: str, pattern: str, keep: int) -> None:
+    """Delete all but the ``keep`` newest checkpoints matching ``pattern`` (no-op for keep <= 0)."""
+    if keep > 0:
+        for stale in checkpoint_paths(save_dir, pattern=pattern)[keep:]:
+            if os.path.lexists(stale):
+                os.remove(stale)
+
+
 def save_checkpoint(args, controller, epoch_itr, val_loss):
+    """Write whatever is due now (see ``planned_files``) and apply the retention flags. The best validation
+    loss lives on as the function attribute ``save_checkpoint.best`` (restored by ``load_checkpoint``)."""
     from hetseq_b200.parallel import distributed_utils
     from hetseq_b200.utils import meters
 
-    prev_best = getattr(save_checkpoint, 'best', val_loss)
+    had_best = hasattr(save_checkpoint, 'best')
+    best_before = save_checkpoint.best if had_best else None
     if val_loss is not None:
-        best_function = max if args.maximize_best_checkpoint_metric else min
-        save_checkpoint.best = best_function(val_loss, prev_best)
-
+        pick = max if args.maximize_best_checkpoint_metric else min
+        save_checkpoint.best = pick(val_loss, best_before if had_best else val_loss)
     if args.no_save:
         return
-    master = distributed_utils.is_master(args)
 
-    def is_better(a, b):
-        return a >= b if args.maximize_best_checkpoint_metric else a <= b
-
-    write_timer = meters.StopwatchMeter()
-    write_timer.start()
-
-    epoch = epoch_itr.epoch
-    end_of_epoch = epoch_itr.end_of_epoch()
-    updates = controller.get_num_updates()
-
-    checkpoint_conds = collections.OrderedDict()
-    checkpoint_conds['checkpoint{}.pt'.format(epoch)] = (
-        end_of_epoch and not args.no_epoch_checkpoints and epoch % args.save_interval == 0)
-    checkpoint_conds['checkpoint_{}_{}.pt'.format(epoch, updates)] = (
-        not end_of_epoch and args.save_interval_updates > 0 and updates % args.save_interval_updates == 0)
-    checkpoint_conds['checkpoint_best.pt'] = (
-        val_loss is not None and
-        (not hasattr(save_checkpoint, 'best') or is_better(val_loss, save_checkpoint.best)))
-    checkpoint_conds['checkpoint_last.pt'] = not args.no_last_checkpoints
-
+    timer = meters.StopwatchMeter()
+    timer.start()
+    epoch, updates, at_end = epoch_itr.epoch, controller.get_num_updates(), epoch_itr.end_of_epoch()
+    # "best" is judged against the value INCLUDING this validation loss, i.e. ties with the running best count
+    names = planned_files(args, epoch, updates, at_end, val_loss, getattr(save_checkpoint, 'best', None))
     extra_state = {'train_iterator': epoch_itr.state_dict(), 'val_loss': val_loss}
     if hasattr(save_checkpoint, 'best'):
-        extra_state.update({'best': save_checkpoint.best})
+        extra_state['best'] = save_checkpoint.best
 
-    checkpoints = [os.path.join(args.save_dir, fn) for fn, cond in checkpoint_conds.items() if cond]
-    if len(checkpoints) > 0:
-        # collective when the optimizer is sharded: every rank calls, rank 0 writes
-        controller.save_checkpoint(checkpoints[0], extra_state)
+    master = distributed_utils.is_master(args)
+    if names:
+        first = os.path.join(args.save_dir, names[0])
+        controller.save_checkpoint(first, extra_state)      # collective with a sharded optimizer; rank 0 writes
         if master:
-            for cp in checkpoints[1:]:
-                shutil.copyfile(checkpoints[0], cp)
-            write_timer.stop()
+            for other in names[1:]:
+                shutil.copyfile(first, os.path.join(args.save_dir, other))
+            timer.stop()
             print('| saved checkpoint {} (epoch {} @ {} updates) (writing took {} seconds)'.format(
-                checkpoints[0], epoch, updates, write_timer.sum))
-    if not master:
-        return
-
-    if not end_of_epoch and args.keep_interval_updates > 0:
-        for old_chk in checkpoint_paths(args.save_dir, pattern=r'checkpoint_\d+_(\d+)\.pt')[args.keep_interval_updates:]:
-            if os.path.lexists(old_chk):
-                os.remove(old_chk)
-    if args.keep_last_epochs > 0:
-        for old_chk in checkpoint_paths(args.save_dir, pattern=r'checkpoint(\d+)\.pt')[args.keep_last_epochs:]:
-            if os.path.lexists(old_chk):
-                os.remove(old_chk)
+                first, epoch, updates, timer.sum))
+    if master:
+        if not at_end:
+            prune(args.save_dir, UPDATES_PATTERN, args.keep_interval_updates)
+        prune(args.save_dir, EPOCH_PATTERN, args.keep_last_epochs)
 
 
 def load_checkpoint(args, controller):
-    """Load a checkpoint (if there is one) and build / restore the training iterator."""
+    """Restore from ``--restore-file`` when it exists and return ``(extra_state, epoch iterator)``; the iterator is
+    positioned where the checkpoint left off unless ``--reset-dataloader``."""
     if args.distributed_rank == 0:
         os.makedirs(args.save_dir, exist_ok=True)
-
-    if args.restore_file in ('checkpoint_last.pt', 'checkpoint_best.pt'):
-        checkpoint_path = os.path.join(args.save_dir, args.restore_file)
-    else:
-        checkpoint_path = args.restore_file
-
-    overrides = args.optimizer_overrides
-    if isinstance(overrides, str):
-        overrides = literal(overrides)
-    extra_state = controller.load_checkpoint(
-        checkpoint_path, args.reset_optimizer, args.reset_lr_scheduler, overrides,
-        reset_meters=args.reset_meters)
-
-    if extra_state is not None and 'best' in extra_state and not args.reset_optimizer and not args.reset_meters:
-        save_checkpoint.best = extra_state['best']
-
-    if extra_state is not None and 'train_iterator' in extra_state and not args.reset_dataloader:
-        itr_state = extra_state['train_iterator']
-        epoch_itr = controller.get_train_iterator(epoch=itr_state['epoch'], load_dataset=True)
-        epoch_itr.load_state_dict(itr_state)
-    else:
-        epoch_itr = controller.get_train_iterator(epoch=0, load_dataset=True)
-
+    in_save_dir = args.restore_file in ('checkpoint_last.pt', 'checkpoint_best.pt')
+    path = os.path.join(args.save_dir, args.restore_file) if in_save_dir else args.restore_file
+    overrides = literal(args.optimizer_overrides) if isinstance(args.optimizer_overrides, str) \
+        else args.optimizer_overrides
+    extra_state = controller.load_checkpoint(path, args.reset_optimizer, args.reset_lr_scheduler, overrides,
+                                             reset_meters=args.reset_meters)
+    extra = extra_state or {}
+    if 'best' in extra and not (args.reset_optimizer or args.reset_meters):
+        save_checkpoint.best = extra['best']
+    position = None if args.reset_dataloader else extra.get('train_iterator')
+    epoch_itr = controller.get_train_iterator(epoch=position['epoch'] if position else 0, load_dataset=True)
+    if position:
+        epoch_itr.load_state_dict(position)
     controller.lr_step(epoch_itr.epoch)
     return extra_state, epoch_itr
 
@@ -133,49 +135,48 @@ def load_checkpoint_to_cpu(path, arg_overrides=None):
     return state
 
 
-def checkpoint_paths(path, pattern=r'checkpoint(\d+)\.pt'):
-    """All checkpoints in ``path`` matching ``pattern``, sorted by the first group, descending."""
-    pt_regexp = re.compile(pattern)
-    entries = []
-    for i, f in enumerate(os.listdir(path)):
-        m = pt_regexp.fullmatch(f)
-        if m is not None:
-            idx = int(m.group(1)) if len(m.groups()) > 0 else i
-            entries.append((idx, m.group(0)))
-    return [os.path.join(path, x[1]) for x in sorted(entries, reverse=True)]
+def checkpoint_paths(path, pattern=EPOCH_PATTERN):
+    """Checkpoints in ``path`` whose name matches ``pattern``, newest first (ordered by the pattern's first group)."""
+    rx = re.compile(pattern)
+    found = []
+    for position, name in enumerate(os.listdir(path)):
+        m = rx.fullmatch(name)
+        if m:
+            found.append((int(m.group(1)) if m.groups() else position, name))
+    found.sort(reverse=True)
+    return [os.path.join(path, name) for _, name in found]
 
 
-def torch_persistent_save(obj, filename):
-    """torch.save with 3 attempts (checkpoint_utils.py:161-167), atomically via rename."""
+def torch_persistent_save(obj, filename, attempts: int = 3):
+    """``torch.save`` with retries like the reference (checkpoint_utils.py:161-167), but through a temporary
+    file that is renamed into place: a crash never leaves a torn ``checkpoint_last.pt``."""
     tmp = '{}.tmp.{}'.format(filename, os.getpid())
-    for i in range(3):
+    for attempt in range(1, attempts + 1):
         try:
             torch.save(obj, tmp)
             os.replace(tmp, filename)
             return True
         except Exception:
-            if i == 2:
+            if attempt == attempts:
                 logging.error(traceback.format_exc())
-                try:
-                    if os.path.exists(tmp):
-                        os.remove(tmp)
-                except OSError:
-                    pass
+    if os.path.exists(tmp):
+        try:
+            os.remove(tmp)
+        except OSError:
+            pass
     return False
 
 
-def convert_state_dict_type(state_dict, ttype=torch.FloatTensor):
-    """Recursively cast every tensor to a CPU float tensor (checkpoint_utils.py:170-181)."""
-    if isinstance(state_dict, dict):
-        cpu_dict = OrderedDict()
-        for k, v in state_dict.items():
-            cpu_dict[k] = convert_state_dict_type(v, ttype)
-        return cpu_dict
-    if isinstance(state_dict, list):
-        return [convert_state_dict_type(v, ttype) for v in state_dict]
-    if torch.is_tensor(state_dict):
-        return state_dict.detach().to('cpu').type(ttype)
-    return state_dict
+def convert_state_dict_type(obj, ttype=torch.FloatTensor):
+    """Copy of a nested state (dicts / lists) with every tensor on the CPU as ``ttype`` (fp32 by default, which is
+    what the reference stores in ``last_optimizer_state``)."""
+    if torch.is_tensor(obj):
+        return obj.detach().to('cpu').type(ttype)
+    if isinstance(obj, dict):
+        return OrderedDict((k, convert_state_dict_type(v, ttype)) for k, v in obj.items())
+    if isinstance(obj, list):
+        return [convert_state_dict_type(v, ttype) for v in obj]
+    return obj
 
 
 def build_state(args, model_state_dict, optimizer_name, optimizer_state, lr_scheduler_state, num_updates,
@@ -206,14 +207,12 @@ def save_state(filename, args, model_state_dict, criterion, optimizer, lr_schedu
 
 
 def verify_checkpoint_directory(save_dir: str) -> None:
-    if not os.path.exists(save_dir):
-        os.makedirs(save_dir, exist_ok=True)
-    temp_file_path = os.path.join(save_dir, 'dummy')
+    """Fail early (before any training) when ``save_dir`` cannot be created or written."""
+    os.makedirs(save_dir, exist_ok=True)
+    probe = os.path.join(save_dir, 'dummy')
     try:
-        with open(temp_file_path, 'w'):
-            pass
-    except OSError as e:
+        open(probe, 'w').close()
+    except OSError:
         print('| Unable to access checkpoint save directory: {}'.format(save_dir))
-        raise e
-    else:
-        os.remove(temp_file_path)
+        raise
+    os.remove(probe)
