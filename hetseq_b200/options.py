@@ -66,7 +66,7 @@ def add_general_args(parser):
     parser.add_argument('--cpu', action='store_true', help='use CPU instead of CUDA')
     parser.add_argument('--log-interval', type=int, default=1, metavar='N',
                         help='log progress every N batches (when progress bar is disabled)')
-    parser.add_argument('--log-format', default='simple', choices=['none', 'simple', 'json'],
+    parser.add_argument('--log-format', default='simple', choices=['none', 'simple', 'json', 'tqdm'],
                         help='log format to use')
     parser.add_argument('--log-file', default=None, metavar='PATH',
                         help='also append one JSON object per logged step to this file')

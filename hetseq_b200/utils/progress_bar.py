@@ -25,6 +25,8 @@ def build_progress_bar(args, iterator, epoch=None, prefix=None, default='simple'
         return noop_progress_bar(iterator, epoch, prefix, log_file)
     if fmt == 'simple':
         return simple_progress_bar(iterator, epoch, prefix, args.log_interval, log_file)
+    if fmt == 'tqdm':
+        return tqdm_progress_bar(iterator, epoch, prefix, log_file)
     raise ValueError('Unknown log format: {}'.format(fmt))
 
 
@@ -185,3 +187,29 @@ class json_progress_bar(progress_bar):
         rec = self._json_record(stats, tag=tag)
         print(json.dumps(rec), flush=True)
         self._sink(rec)
+
+
+class tqdm_progress_bar(progress_bar):
+    """Interactive bar on stderr with the current stats as postfix. The reference lists ``tqdm`` among its log
+    formats but never defines the class (progress_bar.py:24-27); needs the optional ``tqdm`` package."""
+
+    def __init__(self, iterable, epoch=None, prefix=None, log_file=None):
+        super().__init__(iterable, epoch, prefix, log_file)
+        try:
+            from tqdm import tqdm
+        except ImportError as e:
+            raise ImportError('--log-format tqdm needs the tqdm package') from e
+        self.tqdm = tqdm(iterable, self.prefix, leave=False, file=sys.stderr, initial=self.offset,
+                         total=len(iterable) if hasattr(iterable, '__len__') else None)
+
+    def __iter__(self):
+        return iter(self.tqdm)
+
+    def log(self, stats, tag='', step=None):
+        self.tqdm.set_postfix(self._format_stats(stats), refresh=False)
+        if self.log_file:
+            self._sink(self._json_record(stats, step, tag))
+
+    def print(self, stats, tag='', step=None):
+        postfix = self._str_pipes(self._format_stats(stats))
+        self.tqdm.write('{} | {}'.format(self.tqdm.desc, postfix), file=sys.stdout)

@@ -274,3 +274,22 @@ def test_flat_buffer_lazy_zero_grad_and_finalize():
     # padding between parameters is never written
     end_big = buf.offsets[0] + buf.numels[0]
     assert torch.all(buf.flat_grad[end_big:buf.offsets[1]] == 0)
+
+
+def test_tqdm_progress_bar(capsys):
+    """--log-format tqdm (named by the reference, never defined there): iterates everything, epoch summary on stdout."""
+    import argparse
+    pytest.importorskip('tqdm')
+    from hetseq_b200.utils import progress_bar as pb
+    from hetseq_b200.utils.meters import AverageMeter
+    a = argparse.Namespace(log_format='tqdm', log_interval=1, log_file=None, no_progress_bar=False)
+    bar = pb.build_progress_bar(a, list(range(5)), epoch=2)
+    m = AverageMeter()
+    m.update(1.25)
+    seen = []
+    for i in bar:
+        bar.log({'loss': m, 'i': i})
+        seen.append(i)
+    bar.print({'loss': m})
+    assert seen == [0, 1, 2, 3, 4]
+    assert '| epoch 002 | loss 1.250' in capsys.readouterr().out
