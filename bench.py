@@ -59,14 +59,16 @@ def parse():
     ap.add_argument('--no-cuda-graph', dest='cuda_graph', action='store_false')
     ap.add_argument('--bucket-cap-mb', type=int, default=64)
     ap.add_argument('--no-e2e', action='store_true')
+    ap.add_argument('--no-dp-check', action='store_true',
+                    help='skip the untimed multi-GPU correctness check (replica equality, fused vs NCCL backend)')
     return ap.parse_args()
 
 
-def write_config(model_name, tmpdir):
-    cfg = dict(vocab_size=30522, hidden_act='gelu', hidden_dropout_prob=0.1, attention_probs_dropout_prob=0.1,
+def write_config(model_name, tmpdir, dropout=0.1, name='bert_config.json'):
+    cfg = dict(vocab_size=30522, hidden_act='gelu', hidden_dropout_prob=dropout, attention_probs_dropout_prob=dropout,
                max_position_embeddings=512, type_vocab_size=2, initializer_range=0.02)
     cfg.update(MODELS[model_name])
-    path = os.path.join(tmpdir, 'bert_config.json')
+    path = os.path.join(tmpdir, name)
     with open(path, 'w') as f:
         json.dump(cfg, f)
     vocab = os.path.join(tmpdir, 'vocab.txt')
@@ -154,10 +156,12 @@ def make_batches(a, n, vocab, seed):
     return out
 
 
-def timed_loop(step_fn, batches, warmup, steps, world, device):
+def timed_loop(step_fn, batches, warmup, steps, world, device, after_warmup=None):
     import torch
     for i in range(warmup):
         step_fn(batches[i % len(batches)])
+    if after_warmup is not None:
+        after_warmup()
     barrier_sync(world)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
@@ -182,28 +186,33 @@ def run_ours(a):
     from hetseq_b200.ops import lib
     from hetseq_b200.parallel import distributed_utils
 
-    argv = ['--config_file', cfg_path, '--max-sentences', str(a.batch), '--synthetic-data',
-            '--synthetic-seq-len', str(a.seq_len), '--lr', '1e-4', '--warmup-updates', '100',
-            '--total-num-update', '100000', '--weight-decay', '0.01', '--clip-norm', '1.0',
-            '--adam-betas', '(0.9, 0.999)', '--no-save', '--log-format', 'none', '--fast-stat-sync',
-            '--distributed-world-size', str(world), '--distributed-rank', str(rank), '--device-id', str(local),
-            '--dp-backend', a.dp_backend, '--kernels', a.kernels, '--save-dir', tmp,
-            '--bucket-cap-mb', str(a.bucket_cap_mb)]
-    if a.dtype == 'fp16':
-        argv.append('--fp16')
-    elif a.dtype == 'bf16':
-        argv.append('--bf16')
-    if a.cuda_graph:
-        argv.append('--cuda-graph')
-    args = options.make_args('bert', 'adam', 'PolynomialDecayScheduler', argv)
-    if world > 1:
-        args.distributed_init_method = 'env://'
-        distributed_utils.distributed_init(args)
-    torch.manual_seed(args.seed)
-    task = registry.lookup('task', 'bert').setup_task(args)
-    model = task.build_model(args)
-    controller = Controller(args, task, model)
-    controller.optimizer  # build engine
+    def build(cfg, dp_backend, cuda_graph):
+        argv = ['--config_file', cfg, '--max-sentences', str(a.batch), '--synthetic-data',
+                '--synthetic-seq-len', str(a.seq_len), '--lr', '1e-4', '--warmup-updates', '100',
+                '--total-num-update', '100000', '--weight-decay', '0.01', '--clip-norm', '1.0',
+                '--adam-betas', '(0.9, 0.999)', '--no-save', '--log-format', 'none', '--fast-stat-sync',
+                '--distributed-world-size', str(world), '--distributed-rank', str(rank), '--device-id', str(local),
+                '--dp-backend', dp_backend, '--kernels', a.kernels, '--save-dir', tmp,
+                '--bucket-cap-mb', str(a.bucket_cap_mb)]
+        if a.dtype == 'fp16':
+            argv.append('--fp16')
+        elif a.dtype == 'bf16':
+            argv.append('--bf16')
+        if cuda_graph:
+            argv.append('--cuda-graph')
+        args_ = options.make_args('bert', 'adam', 'PolynomialDecayScheduler', argv)
+        if world > 1:
+            args_.distributed_init_method = 'env://'
+            if not torch.distributed.is_initialized():
+                distributed_utils.distributed_init(args_)
+        torch.manual_seed(args_.seed)
+        task_ = registry.lookup('task', 'bert').setup_task(args_)
+        model_ = task_.build_model(args_)
+        ctl = Controller(args_, task_, model_)
+        ctl.optimizer  # build engine
+        return args_, task_, model_, ctl
+
+    args, task, model, controller = build(cfg_path, a.dp_backend, a.cuda_graph)
 
     nb = 8
     host = make_batches(a, nb, model.config.vocab_size, seed=1234 + rank)
@@ -239,10 +248,16 @@ def run_ours(a):
     sampler = ClockSampler(local) if rank == 0 else None
     if sampler:
         sampler.start()
-    ms = timed_loop(step_device, dev, a.warmup, a.steps, world, device)
+    # updates skipped for a non-finite gradient norm are ~1.6 ms cheaper than real ones: count them (the dynamic
+    # loss scale backs off during warm-up; any skip inside the timed region is reported as overflow_steps)
+    mark = {}
+    ms = timed_loop(step_device, dev, a.warmup, a.steps, world, device,
+                    after_warmup=lambda: mark.update(overflow=controller.overflow_updates))
+    overflow_before = mark['overflow']
     if sampler:
         sampler.stop()
     launches_timed = int(launches_per_step * a.steps)
+    overflow_timed = controller.overflow_updates - overflow_before
 
     e2e = None
     if not a.no_e2e:
@@ -251,6 +266,33 @@ def run_ours(a):
         e2e = {'value': round(world * a.batch * a.steps / (ms_e2e / 1e3), 2), 'unit': 'sequences/s',
                'ms_per_step': round(ms_e2e / a.steps, 3), 'h2d_bytes_per_step': int(h2d_bytes),
                'd2h_bytes_per_step': 8 * 8}
+
+    # ---- untimed: is the multi-GPU product correct? ----------------------------------------------------------
+    dp_check = None
+    if world > 1:
+        controller.dp.flush()
+        dp_check = {'params_consistent': bool(controller.dp.check_params_consistent()),
+                    'transport': getattr(controller.dp, 'transport', None)}
+        if not a.no_dp_check and controller.dp.name == 'fused-nvlink':
+            # the same 6 updates (3 eager, capture, replays) from the same initial weights through the fused
+            # NVLink path and through NCCL all-reduce + replicated Adam; dropout off so the two runs see the same
+            # function (dropout sites are numbered per model instance)
+            cfg0, _ = write_config(a.model, tmp, dropout=0.0, name='bert_config_nodrop.json')
+            finals = []
+            for backend, graph in (('nccl', False), (a.dp_backend, a.cuda_graph)):
+                _, t2, _, c2 = build(cfg0, backend, graph)
+                for i in range(6):
+                    c2.train_step([t2.prepare_sample(host[i % len(host)], device)])
+                c2.dp.flush()
+                finals.append((c2.buffer.flat_param[:c2.buffer.used].float().clone(), c2.dp.name,
+                               bool(c2.dp.check_params_consistent())))
+                c2.close()
+                del c2
+                torch.cuda.empty_cache()
+            diff = (finals[0][0] - finals[1][0]).abs()
+            dp_check.update({'max_abs_param_diff_vs_nccl_backend_after_6_updates': float(diff.max()),
+                             'mean_abs_param_diff': float(diff.mean()), 'compared': [finals[0][1], finals[1][1]],
+                             'both_consistent': finals[0][2] and finals[1][2]})
 
     if rank == 0:
         value = world * a.batch * a.steps / (ms / 1e3)
@@ -269,7 +311,10 @@ def run_ours(a):
                        'cuda_graph': bool(a.cuda_graph)},
             'clocks': sampler.summary() if sampler else None,
             'gpu_launches': launches_timed, 'gpu_launches_per_step': launches_per_step,
+            'overflow_steps': int(overflow_timed),
         }
+        if dp_check is not None:
+            out['dp_check'] = dp_check
         if e2e:
             out['e2e'] = e2e
         print(json.dumps(out), flush=True)

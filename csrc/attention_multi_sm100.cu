@@ -100,6 +100,7 @@ attn_fwd_multi_kernel(const __grid_constant__ CUtensorMap tmQKV, const MultiPara
     __syncwarp();
     tmem_alloc(tmem_slot, 256);
   }
+  pdl_sync();   // set-up above overlapped the previous kernel's tail; global memory only from here on
   for (int i = tid; i < P.S; i += MTHREADS) sMask[i] = P.mask[b * P.S + i] * LOG2E;
   tc_fence_before();
   __syncthreads();
@@ -287,6 +288,7 @@ attn_bwd_multi_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_co
     __syncwarp();
     tmem_alloc(tmem_slot, 512);
   }
+  pdl_sync();   // set-up above overlapped the previous kernel's tail; global memory only from here on
   for (int i = tid; i < P.S; i += MTHREADS) sMask[i] = P.mask[b * P.S + i] * LOG2E;
   if (tid < 2 * MD) sBias[tid] = 0.f;
   tc_fence_before();
@@ -533,11 +535,11 @@ int attn_multi_fwd(const void* qkv, const float* mask, void* ctx, float* lse, in
   if (dtype == HS_F16) {
     static bool done = false;
     if (prepare_kernel(attn_fwd_multi_kernel<__half>, MULTI_FWD_SMEM, &done)) return 1;
-    attn_fwd_multi_kernel<__half><<<grid, MTHREADS, MULTI_FWD_SMEM, s>>>(tm, P);
+    (void)launch_k(attn_fwd_multi_kernel<__half>, dim3(grid), dim3(MTHREADS), MULTI_FWD_SMEM, s, tm, P);
   } else if (dtype == HS_BF16) {
     static bool done = false;
     if (prepare_kernel(attn_fwd_multi_kernel<__nv_bfloat16>, MULTI_FWD_SMEM, &done)) return 1;
-    attn_fwd_multi_kernel<__nv_bfloat16><<<grid, MTHREADS, MULTI_FWD_SMEM, s>>>(tm, P);
+    (void)launch_k(attn_fwd_multi_kernel<__nv_bfloat16>, dim3(grid), dim3(MTHREADS), MULTI_FWD_SMEM, s, tm, P);
   } else { set_last_error("hs_attention_fwd: dtype must be f16 or bf16"); return 1; }
   return post_launch("attn_fwd_multi_kernel");
 }
@@ -555,9 +557,9 @@ int attn_multi_bwd(const void* qkv, const float* mask, const void* ctx, const vo
     static bool d0 = false, d1 = false;                                                                  \
     if (prepare_kernel(attn_bwd_multi_kernel<T, 0>, MULTI_BWD_SMEM, &d0)) return 1;                      \
     if (prepare_kernel(attn_bwd_multi_kernel<T, 1>, MULTI_BWD_SMEM, &d1)) return 1;                      \
-    attn_bwd_multi_kernel<T, 0><<<grid, MTHREADS, MULTI_BWD_SMEM, s>>>(tmQ, tmD, P);                     \
+    (void)launch_k(attn_bwd_multi_kernel<T, 0>, dim3(grid), dim3(MTHREADS), MULTI_BWD_SMEM, s, tmQ, tmD, P);                     \
     if (post_launch("attn_bwd_multi_kernel<dKdV>")) return 1;                                            \
-    attn_bwd_multi_kernel<T, 1><<<grid, MTHREADS, MULTI_BWD_SMEM, s>>>(tmQ, tmD, P);                     \
+    (void)launch_k(attn_bwd_multi_kernel<T, 1>, dim3(grid), dim3(MTHREADS), MULTI_BWD_SMEM, s, tmQ, tmD, P);                     \
   } while (0)
   if (dtype == HS_F16) HS_MULTI_BWD(__half);
   else if (dtype == HS_BF16) HS_MULTI_BWD(__nv_bfloat16);

@@ -93,6 +93,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams P) {
     __syncwarp();
     tmem_alloc(tmem_slot, 256);
   }
+  pdl_sync();   // set-up above overlapped the previous kernel's tail; global memory only from here on
   if (tid < AT_S) sMask[tid] = P.mask[b * AT_S + tid] * 1.4426950408889634f;
   tc_fence_before();
   __syncthreads();
@@ -252,6 +253,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     __syncwarp();
     tmem_alloc(tmem_slot, 256);
   }
+  pdl_sync();   // set-up above overlapped the previous kernel's tail; global memory only from here on
   if (tid < AT_S) sMask[tid] = P.mask[b * AT_S + tid] * 1.4426950408889634f;
   if (tid < 3 * AT_D) sBias[tid] = 0.f;
   tc_fence_before();
@@ -471,11 +473,11 @@ extern "C" int hs_attention_fwd(const void* qkv, const float* mask, void* ctx, f
   if (dtype == HS_F16) {
     static bool done = false;
     if (!done) { HS_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATTN_FWD_SMEM)); HS_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<__half>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared)); done = true; }
-    attn_fwd_kernel<__half><<<grid, AT_THREADS, ATTN_FWD_SMEM, s>>>(tm, P);
+    (void)launch_k(attn_fwd_kernel<__half>, dim3(grid), dim3(AT_THREADS), ATTN_FWD_SMEM, s, tm, P);
   } else if (dtype == HS_BF16) {
     static bool done = false;
     if (!done) { HS_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATTN_FWD_SMEM)); HS_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<__nv_bfloat16>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared)); done = true; }
-    attn_fwd_kernel<__nv_bfloat16><<<grid, AT_THREADS, ATTN_FWD_SMEM, s>>>(tm, P);
+    (void)launch_k(attn_fwd_kernel<__nv_bfloat16>, dim3(grid), dim3(AT_THREADS), ATTN_FWD_SMEM, s, tm, P);
   } else { set_last_error("hs_attention_fwd: dtype must be f16 or bf16"); return 1; }
   return post_launch("attn_fwd_kernel");
 }
@@ -503,11 +505,11 @@ extern "C" int hs_attention_bwd(const void* qkv, const float* mask, const void* 
   if (dtype == HS_F16) {
     static bool done = false;
     if (!done) { HS_CUDA_OK(cudaFuncSetAttribute(attn_bwd_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATTN_BWD_SMEM)); HS_CUDA_OK(cudaFuncSetAttribute(attn_bwd_kernel<__half>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared)); done = true; }
-    attn_bwd_kernel<__half><<<grid, AT_THREADS, ATTN_BWD_SMEM, s>>>(tmQ, tmD, P);
+    (void)launch_k(attn_bwd_kernel<__half>, dim3(grid), dim3(AT_THREADS), ATTN_BWD_SMEM, s, tmQ, tmD, P);
   } else if (dtype == HS_BF16) {
     static bool done = false;
     if (!done) { HS_CUDA_OK(cudaFuncSetAttribute(attn_bwd_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATTN_BWD_SMEM)); HS_CUDA_OK(cudaFuncSetAttribute(attn_bwd_kernel<__nv_bfloat16>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared)); done = true; }
-    attn_bwd_kernel<__nv_bfloat16><<<grid, AT_THREADS, ATTN_BWD_SMEM, s>>>(tmQ, tmD, P);
+    (void)launch_k(attn_bwd_kernel<__nv_bfloat16>, dim3(grid), dim3(AT_THREADS), ATTN_BWD_SMEM, s, tmQ, tmD, P);
   } else { set_last_error("hs_attention_bwd: dtype must be f16 or bf16"); return 1; }
   return post_launch("attn_bwd_kernel");
 }

@@ -30,6 +30,19 @@ int  check_cuda(cudaError_t e, const char* what);
 // ----------------------------------------------------------------------------------------------
 // small device helpers
 // ----------------------------------------------------------------------------------------------
+// Programmatic dependent launch (launch attribute programmaticStreamSerialization, see host.h::launch_k):
+// a kernel launched that way may become resident while its predecessor in the stream is still running.
+// Everything before pdl_wait() (barrier init, TMEM allocation, descriptor prefetch) overlaps the predecessor's
+// tail; pdl_wait() returns once the predecessor has completed and its memory is visible, so NO global memory
+// may be touched before it. pdl_launch_dependents() then lets the NEXT kernel do the same to us. Both are
+// no-ops for a kernel launched without the attribute.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_sync() {
+  pdl_wait();
+  pdl_launch_dependents();
+}
+
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }

@@ -180,6 +180,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
   if constexpr (CG == 2) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_sync();   // barriers, TMEM and descriptors are set up; operands of the previous kernel are visible from here on
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -681,7 +682,7 @@ static int launch_gemm(const hs_gemm_args& a, cudaStream_t stream) {
     HS_CUDA_OK(cudaMemsetAsync(a.colsum_out, 0, sizeof(float) * a.N, stream));
   const int work = tiles * p.split_k;
   const int grid = (work < sms ? work : sms) * CG;
-  kern<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, tmC, tmAux, p);
+  (void)launch_k(kern, dim3(grid), dim3(GEMM_THREADS), Cfg::SMEM_BYTES, stream, tmA, tmB, tmC, tmAux, p);
   return post_launch("gemm_tcgen05_kernel");
 }
 

@@ -45,6 +45,7 @@ struct LnFwdParams {
 
 template <typename T, int NV>
 __global__ void __launch_bounds__(LN_THREADS) ln_fwd_kernel(LnFwdParams P) {
+  pdl_sync();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * LN_ROWS_PER_BLOCK + warp;
   if (row >= P.M) return;
@@ -121,136 +122,6 @@ __global__ void __launch_bounds__(LN_THREADS) ln_fwd_kernel(LnFwdParams P) {
   }
 }
 
-// Streaming variant of the forward kernel (same structure as ln_bwd_kernel below): persistent, one CTA per SM,
-// each warp streams its rows of x (and of the residual) through a ring of bulk-copied shared-memory slots, so the
-// loads of up to STAGES rows per warp are in flight without occupying registers. Selected by
-// HETSEQ_LN_FWD_STREAM=1. Measured on BERT-large B=32 S=128: passes the same numerics tests, but the step is
-// slower with it (13.78 vs 13.58 ms), so ln_fwd_kernel stays the default.
-constexpr int LNF_WARPS = 8;
-constexpr int LNF_THREADS = LNF_WARPS * 32;
-
-template <typename T, int NV, int STAGES>
-__global__ void __launch_bounds__(LNF_THREADS, 1) ln_fwd_stream_kernel(LnFwdParams P, uint32_t bar_offset) {
-  extern __shared__ __align__(128) uint8_t lnf_smem[];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int nvec = P.H >> 3;
-  const uint32_t row_bytes = static_cast<uint32_t>(P.H) * sizeof(T);
-  const bool has_res = P.residual != nullptr;
-  uint8_t* ring = lnf_smem + static_cast<size_t>(warp) * STAGES * 2 * row_bytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(lnf_smem + bar_offset) + warp * STAGES;
-  const bool drop = P.p > 0.f;
-  const float scale = drop ? 1.f / (1.f - P.p) : 1.f;
-  const uint64_t seed = drop ? philox_seed(P.seed) : 0ull;
-  const uint32_t thr = dropout_thr16(P.p);
-  const int gw = blockIdx.x * LNF_WARPS + warp, GW = gridDim.x * LNF_WARPS;
-
-  auto issue = [&](int slot, long long row) {
-    mbar_expect_tx(&bars[slot], (has_res ? 2 : 1) * row_bytes);
-    bulk_load_1d(ring + (2 * slot) * row_bytes, reinterpret_cast<const T*>(P.x) + row * P.H, row_bytes, &bars[slot]);
-    if (has_res)
-      bulk_load_1d(ring + (2 * slot + 1) * row_bytes, reinterpret_cast<const T*>(P.residual) + row * P.H, row_bytes,
-                   &bars[slot]);
-  };
-  if (lane == 0) {
-#pragma unroll
-    for (int s = 0; s < STAGES; ++s) mbar_init(&bars[s], 1);
-    fence_mbar_init();
-#pragma unroll
-    for (int s = 0; s < STAGES; ++s) {
-      const long long row = gw + static_cast<long long>(s) * GW;
-      if (row < P.M) issue(s, row);
-    }
-  }
-  __syncwarp();
-
-  uint4 gpk[NV], bpk[NV];
-#pragma unroll
-  for (int j = 0; j < NV; ++j) {
-    const int vi = j * 32 + lane;
-    gpk[j] = vi < nvec ? reinterpret_cast<const uint4*>(P.gamma)[vi] : make_uint4(0, 0, 0, 0);
-    bpk[j] = vi < nvec ? reinterpret_cast<const uint4*>(P.beta)[vi] : make_uint4(0, 0, 0, 0);
-  }
-
-  int stage = 0;
-  uint32_t phase = 0;
-  for (long long row = gw; row < P.M; row += GW) {
-    mbar_wait(&bars[stage], phase);
-    const uint4* sx = reinterpret_cast<const uint4*>(ring + (2 * stage) * row_bytes);
-    const uint4* sr = reinterpret_cast<const uint4*>(ring + (2 * stage + 1) * row_bytes);
-    float v[NV][8];
-    float sum = 0.f;
-#pragma unroll
-    for (int j = 0; j < NV; ++j) {
-      const int vi = j * 32 + lane;
-      if (vi < nvec) {
-        float f[8];
-        unpack8<T>(sx[vi], f);
-        if (P.bias) {
-          float b[8];
-          unpack8<T>(reinterpret_cast<const uint4*>(P.bias)[vi], b);
-#pragma unroll
-          for (int k = 0; k < 8; ++k) f[k] += b[k];
-        }
-        if (drop && !P.post_dropout) {
-          float mk[8];
-          philox_keep8(seed, P.site, (static_cast<uint64_t>(row) * P.H + vi * 8) >> 3, thr, scale, mk);
-#pragma unroll
-          for (int k = 0; k < 8; ++k) f[k] *= mk[k];
-        }
-        if (has_res) {
-          float r[8];
-          unpack8<T>(sr[vi], r);
-#pragma unroll
-          for (int k = 0; k < 8; ++k) f[k] += r[k];
-        }
-        if (P.z) reinterpret_cast<uint4*>(reinterpret_cast<T*>(P.z) + static_cast<size_t>(row) * P.H)[vi] = pack8<T>(f);
-#pragma unroll
-        for (int k = 0; k < 8; ++k) { v[j][k] = f[k]; sum += f[k]; }
-      }
-    }
-    // the slot is consumed: refill it with the row STAGES rounds ahead
-    __syncwarp();
-    if (lane == 0) {
-      const long long nxt = row + static_cast<long long>(STAGES) * GW;
-      if (nxt < P.M) issue(stage, nxt);
-    }
-    if (++stage == STAGES) { stage = 0; phase ^= 1; }
-    const float mean = warp_sum(sum) / P.H;
-    float sq = 0.f;
-#pragma unroll
-    for (int j = 0; j < NV; ++j) {
-      if (j * 32 + lane < nvec) {
-#pragma unroll
-        for (int k = 0; k < 8; ++k) { const float d = v[j][k] - mean; sq += d * d; }
-      }
-    }
-    const float rstd = rsqrtf(warp_sum(sq) / P.H + P.eps);
-    if (lane == 0) {
-      if (P.mean) P.mean[row] = mean;
-      if (P.rstd) P.rstd[row] = rstd;
-    }
-    T* y = reinterpret_cast<T*>(P.y) + static_cast<size_t>(row) * P.H;
-#pragma unroll
-    for (int j = 0; j < NV; ++j) {
-      const int vi = j * 32 + lane;
-      if (vi < nvec) {
-        float g[8], b[8], o[8];
-        unpack8<T>(gpk[j], g);
-        unpack8<T>(bpk[j], b);
-#pragma unroll
-        for (int k = 0; k < 8; ++k) o[k] = g[k] * ((v[j][k] - mean) * rstd) + b[k];
-        if (drop && P.post_dropout) {
-          float mk[8];
-          philox_keep8(seed, P.site, (static_cast<uint64_t>(row) * P.H + vi * 8) >> 3, thr, scale, mk);
-#pragma unroll
-          for (int k = 0; k < 8; ++k) o[k] *= mk[k];
-        }
-        reinterpret_cast<uint4*>(y)[vi] = pack8<T>(o);
-      }
-    }
-  }
-}
-
 struct LnBwdParams {
   const void* dy; const void* z; const void* gamma; const float* mean; const float* rstd;
   void* dz;       // gradient w.r.t. z (the residual path), 16-bit
@@ -287,6 +158,9 @@ __global__ void __launch_bounds__(LNB_THREADS, 1) ln_bwd_kernel(LnBwdParams P, u
 #pragma unroll
     for (int s = 0; s < LNB_STAGES; ++s) mbar_init(&bars[s], 1);
     fence_mbar_init();
+  }
+  pdl_sync();   // dy / z of the previous kernel are visible from here on
+  if (lane == 0) {
 #pragma unroll
     for (int s = 0; s < LNB_STAGES; ++s) {
       const long long row = gw + static_cast<long long>(s) * GW;
@@ -470,44 +344,12 @@ extern "C" int hs_ln_fwd(const void* x, const void* bias, const void* residual, 
   const int grid = (M + LN_ROWS_PER_BLOCK - 1) / LN_ROWS_PER_BLOCK;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const int nv = (H + 255) / 256;
-  static const bool stream_variant = [] { const char* e = getenv("HETSEQ_LN_FWD_STREAM"); return e != nullptr && atoi(e) != 0; }();
-  const bool aligned = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(residual)) % 16) == 0;
-  if (stream_variant && aligned && nv <= 4 && M >= 64) {
-    constexpr int ST = 4;
-    const size_t ring = static_cast<size_t>(LNF_WARPS) * ST * 2 * H * 2;
-    const size_t smem = ring + LNF_WARPS * ST * sizeof(uint64_t);
-    const int rows_blocks = (M + LNF_WARPS - 1) / LNF_WARPS;
-    const int g2 = rows_blocks < num_sms() ? rows_blocks : num_sms();
-#define HS_LN_FWD_STREAM_ONE(T, NVV)                                                                                   \
-  do {                                                                                                                 \
-    static bool attr_done[64] = {false};                                                                               \
-    int dev = 0;                                                                                                       \
-    HS_CUDA_OK(cudaGetDevice(&dev));                                                                                   \
-    if (dev < 64 && !attr_done[dev]) {                                                                                 \
-      HS_CUDA_OK(cudaFuncSetAttribute(ln_fwd_stream_kernel<T, NVV, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024)); \
-      attr_done[dev] = true;                                                                                           \
-    }                                                                                                                  \
-    ln_fwd_stream_kernel<T, NVV, ST><<<g2, LNF_THREADS, smem, s>>>(P, static_cast<uint32_t>(ring));                    \
-  } while (0)
-#define HS_LN_FWD_STREAM(T)                                \
-  do {                                                     \
-    if (nv <= 1) HS_LN_FWD_STREAM_ONE(T, 1);               \
-    else if (nv <= 2) HS_LN_FWD_STREAM_ONE(T, 2);          \
-    else HS_LN_FWD_STREAM_ONE(T, 4);                       \
-  } while (0)
-    if (dtype == HS_F16) HS_LN_FWD_STREAM(__half);
-    else if (dtype == HS_BF16) HS_LN_FWD_STREAM(__nv_bfloat16);
-    else { set_last_error("hs_ln_fwd: dtype must be f16 or bf16"); return 1; }
-#undef HS_LN_FWD_STREAM
-#undef HS_LN_FWD_STREAM_ONE
-    return post_launch("ln_fwd_stream_kernel");
-  }
 #define HS_LN_FWD(T)                                                                 \
   do {                                                                               \
-    if (nv <= 1) ln_fwd_kernel<T, 1><<<grid, LN_THREADS, 0, s>>>(P);                 \
-    else if (nv <= 2) ln_fwd_kernel<T, 2><<<grid, LN_THREADS, 0, s>>>(P);            \
-    else if (nv <= 4) ln_fwd_kernel<T, 4><<<grid, LN_THREADS, 0, s>>>(P);            \
-    else ln_fwd_kernel<T, 8><<<grid, LN_THREADS, 0, s>>>(P);                         \
+    if (nv <= 1) (void)launch_k(ln_fwd_kernel<T, 1>, dim3(grid), dim3(LN_THREADS), 0, s, P);                 \
+    else if (nv <= 2) (void)launch_k(ln_fwd_kernel<T, 2>, dim3(grid), dim3(LN_THREADS), 0, s, P);            \
+    else if (nv <= 4) (void)launch_k(ln_fwd_kernel<T, 4>, dim3(grid), dim3(LN_THREADS), 0, s, P);            \
+    else (void)launch_k(ln_fwd_kernel<T, 8>, dim3(grid), dim3(LN_THREADS), 0, s, P);                         \
   } while (0)
   if (dtype == HS_F16) HS_LN_FWD(__half);
   else if (dtype == HS_BF16) HS_LN_FWD(__nv_bfloat16);
@@ -553,7 +395,7 @@ extern "C" int hs_ln_bwd(const void* dy, const void* z, const void* gamma, const
       HS_CUDA_OK(cudaFuncSetAttribute(ln_bwd_kernel<T, NVV, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024)); \
       attr_done[dev] = true;                                                                           \
     }                                                                                                  \
-    ln_bwd_kernel<T, NVV, ST><<<grid, LNB_THREADS, smem, s>>>(P, static_cast<uint32_t>(bar_offset));                                    \
+    (void)launch_k(ln_bwd_kernel<T, NVV, ST>, dim3(grid), dim3(LNB_THREADS), smem, s, P, static_cast<uint32_t>(bar_offset));                                    \
   } while (0)
 #define HS_LN_BWD(T)                                  \
   do {                                                \

@@ -6,6 +6,7 @@
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <mutex>
 
 namespace hs {
@@ -37,6 +38,14 @@ int post_launch(const char* kernel) {
     return 1;
   }
   return 0;
+}
+
+bool pdl_enabled() {
+  static const bool on = []() {
+    const char* e = getenv("HETSEQ_PDL");
+    return !(e != nullptr && e[0] == '0');
+  }();
+  return on;
 }
 
 int num_sms() {

@@ -4,9 +4,12 @@
 // [B*S, 30522] and the NSP logits [B, 2] (bert_modeling.py:881-886). ATen runs
 // log_softmax + nll_loss forward, then materialises a second [rows, V] tensor in backward. Here one
 // block per row makes two passes over the (L2-resident) row: online max / sum-exp, then it overwrites
-// the logits IN PLACE with d(loss)/d(logits) = (softmax - onehot) / n_valid, zeroing ignored rows and
-// the pad columns [V, ld). The scalar upstream gradient is applied later through the decoder GEMMs'
-// alpha_dev, so the [rows, V] tensor is touched exactly twice overall. The MLM head only ever sees
+// the logits IN PLACE with d(loss)/d(logits), zeroing ignored rows and the pad columns [V, ld). By default
+// that is (softmax - onehot) / n_valid; with inv_count_out the 1/n_valid is NOT applied to the stored values
+// but written to a device scalar for the consumer to fold into its accumulator scale: the stored entries are
+// then O(1) instead of O(1/n_valid), which matters in fp16 (with ~600 labelled rows and V = 30522 almost the
+// whole tail of softmax/n_valid is subnormal or flushes to zero). The scalar upstream gradient is applied
+// later through the decoder GEMMs' alpha_dev, so the [rows, V] tensor is touched exactly twice overall. The MLM head only ever sees
 // the labelled rows (hs_gather_rows / hs_scatter_add_rows implement SURVEY.md Q21 / W9).
 #include "common.cuh"
 #include "host.h"
@@ -38,14 +41,14 @@ __device__ __forceinline__ float block_reduce_max(float v, float* red) {
 template <typename T, typename LabelT>
 __global__ void __launch_bounds__(XE_THREADS)
 xent_fwd_bwd_kernel(T* __restrict__ logits, int ld, const LabelT* __restrict__ labels, int rows, int V,
-                    float* __restrict__ row_loss, int write_grad) {
+                    float* __restrict__ row_loss, int write_grad, int normalize) {
   __shared__ float red[32];
   const int row = blockIdx.x;
   // number of valid rows (same value in every block; labels is tiny)
   float cnt = 0.f;
   for (int i = threadIdx.x; i < rows; i += blockDim.x) cnt += (labels[i] >= 0) ? 1.f : 0.f;
   cnt = block_reduce_sum(cnt, red);
-  const float inv_n = cnt > 0.f ? 1.f / cnt : 0.f;
+  const float inv_n = normalize ? (cnt > 0.f ? 1.f / cnt : 0.f) : 1.f;
 
   T* x = logits + static_cast<size_t>(row) * ld;
   const long long label = static_cast<long long>(labels[row]);
@@ -109,7 +112,7 @@ xent_fwd_bwd_kernel(T* __restrict__ logits, int ld, const LabelT* __restrict__ l
 template <typename LabelT>
 __global__ void __launch_bounds__(XE_THREADS)
 xent_finalize_kernel(const float* __restrict__ row_loss, const LabelT* __restrict__ labels, int rows,
-                     float* __restrict__ loss, int accumulate) {
+                     float* __restrict__ loss, int accumulate, float* __restrict__ inv_count_out) {
   __shared__ float red[32];
   float s = 0.f, c = 0.f;
   for (int i = threadIdx.x; i < rows; i += blockDim.x) {
@@ -120,7 +123,8 @@ xent_finalize_kernel(const float* __restrict__ row_loss, const LabelT* __restric
   c = block_reduce_sum(c, red);
   if (threadIdx.x == 0) {
     const float v = c > 0.f ? s / c : 0.f;
-    loss[0] = accumulate ? loss[0] + v : v;
+    if (loss != nullptr) loss[0] = accumulate ? loss[0] + v : v;
+    if (inv_count_out != nullptr) inv_count_out[0] = c > 0.f ? 1.f / c : 0.f;
   }
 }
 
@@ -164,7 +168,8 @@ scatter_add_rows_kernel(const uint4* __restrict__ src, const IdxT* __restrict__ 
 using namespace hs;
 
 extern "C" int hs_xent(void* logits, int ld, const void* labels, int label_is_i64, int rows, int V, float* row_loss,
-                       float* loss, int accumulate_loss, int write_grad, int dtype, hs_stream_t stream) {
+                       float* loss, int accumulate_loss, int write_grad, float* inv_count_out, int dtype,
+                       hs_stream_t stream) {
   if (rows <= 0 || V <= 0 || ld < V || ld % 8 != 0 || (reinterpret_cast<uintptr_t>(logits) % 16) != 0) {
     set_last_error("hs_xent: bad arguments rows=%d V=%d ld=%d (ld must be a multiple of 8, >= V; base 16B aligned)", rows, V, ld);
     return 1;
@@ -172,10 +177,10 @@ extern "C" int hs_xent(void* logits, int ld, const void* labels, int label_is_i6
   cudaStream_t s = static_cast<cudaStream_t>(stream);
 #define HS_XENT(T, L)                                                                                           \
   do {                                                                                                          \
-    xent_fwd_bwd_kernel<T, L><<<rows, XE_THREADS, 0, s>>>((T*)logits, ld, (const L*)labels, rows, V, row_loss, write_grad); \
+    xent_fwd_bwd_kernel<T, L><<<rows, XE_THREADS, 0, s>>>((T*)logits, ld, (const L*)labels, rows, V, row_loss, write_grad, inv_count_out == nullptr ? 1 : 0); \
     if (post_launch("xent_fwd_bwd_kernel")) return 1;                                                           \
-    if (loss) {                                                                                                 \
-      xent_finalize_kernel<L><<<1, XE_THREADS, 0, s>>>(row_loss, (const L*)labels, rows, loss, accumulate_loss);  \
+    if (loss || inv_count_out) {                                                                                \
+      xent_finalize_kernel<L><<<1, XE_THREADS, 0, s>>>(row_loss, (const L*)labels, rows, loss, accumulate_loss, inv_count_out);  \
       if (post_launch("xent_finalize_kernel")) return 1;                                                        \
     }                                                                                                           \
   } while (0)

@@ -72,6 +72,12 @@ class Controller(object):
         self._static_sample = None
         self._static_sample, self._static_out = None, None
         self._stats_host = None
+        #: updates skipped because of non-finite gradients (fp16 loss scaling); bench.py reports it
+        self.overflow_updates = 0
+        if self._graph_enabled and getattr(args, 'max_sentences', None):
+            # static shapes: short last batches and padding batches are grown to full size on the host
+            if hasattr(task, 'static_batch_size'):
+                task.static_batch_size = int(args.max_sentences)
         self.init_meters(args)
 
     # -- meters -----------------------------------------------------------------------------------
@@ -177,6 +183,7 @@ class Controller(object):
         """Write all training state to ``filename``. Every rank must call this when the optimizer
         is sharded (state gathering is collective); only the master writes."""
         extra_state['train_meters'] = self.meters
+        self.dp.flush()      # an update that is still riding next to the forward pass must land first
         opt_state = None
         if not self.args.no_save_optimizer_state:
             if getattr(self.optimizer, 'sharded', False) or distributed_utils.is_master(self.args):
@@ -191,6 +198,8 @@ class Controller(object):
                         optimizer_overrides=None, reset_meters=False):
         """Load all training state from a checkpoint file (every rank reads the file itself)."""
         extra_state, self._optim_history, last_optim_state = None, [], None
+        if self._dp is not None:
+            self._dp.flush()
 
         if os.path.exists(filename):
             state = checkpoint_utils.load_checkpoint_to_cpu(filename)
@@ -280,7 +289,14 @@ class Controller(object):
         Device work and host bookkeeping are separated: ``_device_step`` only queues work (no host
         synchronisation, no host values that change between updates baked into kernels), which is what
         allows ``--cuda-graph`` to capture it once and replay it; the host then makes ONE read of a small
-        result vector and updates meters, loss scale and the LR schedule."""
+        result vector and updates meters, loss scale and the LR schedule.
+
+        Every rank queues the same cross-rank operations in the same order whether it replays the graph or
+        runs eagerly (with the fused backend: in-kernel reduce-scatter, norm + sample-size exchange and update;
+        the statistics all-reduce comes after the step in both modes), so an odd batch on one rank -- a padding
+        batch of an uneven shard, a short last batch -- never needs agreement between ranks. Such batches are
+        padded to the static shapes and weighted on the device (weight 0 for a padding batch), the invariant of
+        the reference's dummy-batch handling (controller.py:237-241)."""
         if self._dummy_batch is None:
             self._dummy_batch = samples[0]
 
@@ -300,7 +316,7 @@ class Controller(object):
             if ignore:
                 # uneven shards: run on the cached dummy batch and ignore its gradients so that every rank
                 # still takes part in the reduction (controller.py:237-241)
-                p = self._prepare_sample(self._dummy_batch)
+                p = self._prepare_sample(self._dummy_batch, allow_host)
             sample_dev, stats = p
             prepared.append((sample_dev, stats, ignore))
             if not ignore:
@@ -309,30 +325,31 @@ class Controller(object):
                 host_stats[2] += stats[1]
 
         # ---- device ---------------------------------------------------------------------------------
-        graphable = (self._graph_enabled and not dummy_batch and len(prepared) == 1 and not prepared[0][2])
+        graphable = self._graph_enabled and not dummy_batch and len(prepared) == 1
         try:
+            if dummy_batch:
+                # forward + backward only, like the reference, which returns before stats / clip / step
+                # (controller.py:288-289); nothing is reduced and nothing is applied
+                self._device_step(prepared, host_stats, update=False)
+                return None
             if graphable:
-                readback = self._graphed_device_step(prepared[0], host_stats)
+                readback, reduced = self._graphed_device_step(prepared[0], host_stats)
             else:
-                readback = self._device_step(prepared, host_stats, device_stats_sync=True)
+                readback, reduced = self._device_step(prepared, host_stats)
         except RuntimeError as e:
             if 'out of memory' in str(e):
                 raise RuntimeError('ran out of memory with exception') from e
             raise
-        if dummy_batch:
-            return None
 
         # ---- the single device->host read of the update --------------------------------------------------
-        if graphable and self._sync_stats():
-            # inside a captured graph the sample size is taken as world x local (all ranks hold full
-            # batches); the logging statistics are summed here, outside the graph
-            comm = readback[:6].clone()
-            torch.distributed.all_reduce(comm)
-            readback = torch.cat([comm, readback[6:]])
+        if not reduced and self._sync_stats():
+            readback = self._reduce_logging_stats(readback)
         sample_size, nsentences, loss_total, nll_total, ntokens, ooms, gnorm, skip = readback.tolist()
         opt = self.optimizer
         logging_output = None
         try:
+            if skip and opt.scaler is not None:
+                self.overflow_updates += 1
             opt.finish_update(bool(skip) and opt.scaler is not None)
             self.set_num_updates(self.get_num_updates() + 1)
             every = int(getattr(self.args, 'check_params_interval', 0) or 0)
@@ -367,22 +384,70 @@ class Controller(object):
         self.meters['train_wall'].stop()
         return logging_output
 
-    def _device_step(self, prepared, host_stats, device_stats_sync=True):
-        """Queue one whole update on the device and return the 8-element result vector
-        [sample_size, nsentences, loss_sum, nll_sum, ntokens, ooms, grad_norm, overflow] (fp64, device)."""
+    def _reduce_logging_stats(self, readback):
+        """Sum [sample_size, nsentences, loss, nll_loss, ntokens, ooms] over ranks (controller.py:292-334).
+        With ``--fast-stat-sync`` one 48-byte all-reduce; otherwise the general path: gather every rank's
+        numbers, aggregate them (the reference gathers and then forgets to aggregate) and run the cross-rank
+        gradient-norm consistency check on the previous step's norm (controller.py:325-328)."""
+        stats = readback[:6]
+        if self.fast_stat_sync:
+            comm = stats.clone() if stats.device == distributed_utils.comm_device() else stats.cpu()
+            torch.distributed.all_reduce(comm)
+            stats = comm.to(self.device)
+        else:
+            gathered = distributed_utils.all_gather_list([stats.tolist(), self._prev_grad_norm])
+            prev_norms = [g[1] for g in gathered]
+            assert (all(n == prev_norms[0] for n in prev_norms)
+                    or all(n is None or math.isnan(n) or math.isinf(n) for n in prev_norms)), \
+                'Fatal error: gradients are inconsistent between workers'
+            stats = torch.tensor([sum(g[0][k] for g in gathered) for k in range(6)],
+                                 dtype=torch.float64, device=self.device)
+        return torch.cat([stats, readback[6:]])
+
+    def _device_step(self, prepared, host_stats, update=True, static_weight=False):
+        """Queue one whole update on the device. Returns (the 8-element result vector [sample_size, nsentences,
+        loss_sum, nll_sum, ntokens, ooms, grad_norm, overflow] (fp64, device), whether its first six entries
+        are already summed over ranks)."""
         model, dp, opt = self._model, self.dp, self.optimizer
+        fused = bool(getattr(dp, 'fused', False))
+        multi = self._sync_stats()
         self.zero_grad()
         marks = [self._mark()] if (self._phase_timing and not self._capturing) else None
+        # host integers travel through a pinned staging vector (re-read by a captured graph on each replay)
+        if self._stats_host is None:
+            self._stats_host = torch.zeros(6, dtype=torch.float64)
+            if self.cuda:
+                self._stats_host = self._stats_host.pin_memory()
+        self._stats_host[0], self._stats_host[1], self._stats_host[4] = host_stats[0], host_stats[1], host_stats[2]
+        stats_in = self._stats_host.to(self.device, non_blocking=True)
+        batch_mode = self.args.sample_size_mode == 'batch'
         loss_sum = torch.zeros((), dtype=torch.float32, device=self.device)
-        dp.begin_update(len(prepared))
+        if update:
+            dp.begin_update(len(prepared))
         for i, (sample_dev, stats, ignore_grad) in enumerate(prepared):
-            dp.begin_micro_batch(i, is_last=(i == len(prepared) - 1))
+            if len(prepared) > 1:
+                from hetseq_b200.ops import rng
+                rng.set_micro_batch(i)        # fresh dropout masks per micro-batch, like the reference
+            if update:
+                dp.begin_micro_batch(i, is_last=(i == len(prepared) - 1))
+            else:
+                opt.buffer.reset_ready_counts()
+            weight = None
+            if static_weight:
+                # captured graph: the weight of the (single) micro-batch is read from device memory -- the number
+                # of real sentences (0 for a padding batch), or 1/0 in 'reference' mode
+                weight = (stats_in[1] if batch_mode else (stats_in[1] > 0).to(torch.float64)).to(torch.float32)
+                ignore_grad = False
             with nvtx.range('fwd+bwd micro-batch'):
                 loss, sample_size, logging_output = self.task.train_step(sample_dev, model, opt, ignore_grad,
-                                                                         stats=stats)
-            if not ignore_grad:
-                weight = logging_output.get('nsentences', 1) if self.args.sample_size_mode == 'batch' else 1.0
-                loss_sum = loss_sum + logging_output['loss'].float() * weight
+                                                                         stats=stats, weight=weight)
+            if weight is not None:
+                loss_sum = loss_sum + logging_output['loss'].float() * (weight if batch_mode else (weight > 0).float())
+            elif not ignore_grad:
+                w = logging_output.get('nsentences', 1) if batch_mode else 1.0
+                loss_sum = loss_sum + logging_output['loss'].float() * w
+        if not update:
+            return None, False
         if marks is not None:
             marks.append(self._mark())      # forward + backward enqueued
         opt.buffer.finalize_grads()
@@ -392,44 +457,23 @@ class Controller(object):
             marks.append(self._mark())      # gradient reduction complete
 
         # ---- stats: [sample_size, nsentences, loss, nll_loss, ntokens, ooms] like controller.py:292-314
-        multi = self._sync_stats()
-        # host integers travel through a pinned staging vector (re-read by a captured graph on each replay)
-        if self._stats_host is None:
-            self._stats_host = torch.zeros(6, dtype=torch.float64)
-            if self.cuda:
-                self._stats_host = self._stats_host.pin_memory()
-        self._stats_host[0], self._stats_host[1], self._stats_host[4] = host_stats[0], host_stats[1], host_stats[2]
-        stats_vec = self._stats_host.to(self.device, non_blocking=True)
         loss64 = loss_sum.double()
-        stats_vec = torch.cat([stats_vec[:2], loss64.reshape(1), loss64.reshape(1), stats_vec[4:]])
-        world = float(self.args.distributed_world_size if multi else 1)
-        if multi and device_stats_sync:
-            if self.fast_stat_sync:
-                comm = stats_vec if stats_vec.device == distributed_utils.comm_device() else stats_vec.cpu()
-                torch.distributed.all_reduce(comm)
-                stats_vec = comm.to(self.device)
-            else:
-                # general path: gather every rank's logging outputs, aggregate them (the reference
-                # gathers and then forgets to aggregate, controller.py:315-334), and run the
-                # cross-rank gradient-norm consistency check on the previous step's norm
-                host = stats_vec.tolist()
-                gathered = distributed_utils.all_gather_list([host, self._prev_grad_norm])
-                prev_norms = [g[1] for g in gathered]
-                assert (all(n == prev_norms[0] for n in prev_norms)
-                        or all(n is None or math.isnan(n) or math.isinf(n) for n in prev_norms)), \
-                    'Fatal error: gradients are inconsistent between workers'
-                stats_vec = torch.tensor([sum(g[0][k] for g in gathered) for k in range(6)],
-                                         dtype=torch.float64, device=self.device)
-            sample_size_dev = stats_vec[0]
-        elif multi:
-            sample_size_dev = stats_vec[0] * world     # captured graph: all ranks hold equal, full batches
+        stats_vec = torch.cat([stats_in[:2], loss64.reshape(1), loss64.reshape(1), stats_in[4:]])
+        reduced = False
+        if fused:
+            # the ranks' sample sizes are summed inside the norm-exchange kernel: no collective, no host read
+            opt.set_grad_denominator(stats_vec[0])
         else:
+            world = 1.0
+            if multi:
+                stats_vec = self._reduce_logging_stats(torch.cat([stats_vec, stats_vec[:2]]))[:6]
+                reduced = True
+                world = float(self.args.distributed_world_size)
             sample_size_dev = stats_vec[0]
-
-        # normalise grads by sample size (controller.py:338-339); the backend already made them the mean
-        # over ranks, so the factor is world / sample_size like the reference's
-        opt.multiply_grads(torch.where(sample_size_dev > 0, world / sample_size_dev.clamp(min=1e-12),
-                                       torch.ones_like(sample_size_dev)).float())
+            # normalise grads by sample size (controller.py:338-339); the backend already made them the mean
+            # over ranks, so the factor is world / sample_size like the reference's
+            opt.multiply_grads(torch.where(sample_size_dev > 0, world / sample_size_dev.clamp(min=1e-12),
+                                           torch.ones_like(sample_size_dev)).float())
         with nvtx.range('grad norm + clip'):
             grad_norm = opt.clip_grad_norm(self.args.clip_norm)
         if marks is not None:
@@ -440,22 +484,24 @@ class Controller(object):
             marks.append(self._mark())      # update (+ all-gather)
             self._phase_events.append(marks)
         skip = opt._skip.double().reshape(1) if opt._skip is not None else torch.zeros(1, dtype=torch.float64, device=self.device)
-        return torch.cat([stats_vec, grad_norm.detach().double().reshape(1), skip])
+        return torch.cat([stats_vec, grad_norm.detach().double().reshape(1), skip]), reduced
 
     # -- CUDA graph capture of the device step -----------------------------------------------------------
     def _graphed_device_step(self, prepared_one, host_stats):
         """Replay (after a few eager warm-up updates: capture) the whole device step as one CUDA graph.
         Inputs are copied into static buffers; per-update scalars (lr, bias correction, loss scale, dropout
-        seed, NVLink epoch) live in device memory that the graph re-reads."""
-        sample_dev, stats, _ = prepared_one
-        key = tuple((tuple(t.shape), t.dtype) for t in sample_dev) + (tuple(host_stats[:2]),)
+        seed, NVLink epoch, batch weight) live in device memory that the graph re-reads."""
+        sample_dev, stats, ignore = prepared_one
+        key = tuple((tuple(t.shape), t.dtype) for t in sample_dev)
         if self._graph is not None and key != self._graph_key:
-            prepared_one = (self.task.prepare_sample(sample_dev, self.device), stats, False)
-            return self._device_step([prepared_one], host_stats, device_stats_sync=True)   # odd-shaped batch: eager
+            # a batch that does not fit the captured shapes: eager (same cross-rank operations, so peers that
+            # replay their graph are not disturbed)
+            prepared_one = (self.task.prepare_sample(sample_dev, self.device), stats, ignore)
+            return self._device_step([prepared_one], host_stats)
         if self._graph is None:
             self._graph_warmup += 1
-            if self._graph_warmup <= 3:
-                return self._device_step([prepared_one], host_stats, device_stats_sync=True)
+            if self._graph_warmup <= 3 or ignore:
+                return self._device_step([prepared_one], host_stats)
             # capture
             self._graph_key = key
             if isinstance(sample_dev, PackedSample):
@@ -469,11 +515,11 @@ class Controller(object):
             try:
                 # capture on a HIGH-priority stream: kernel nodes inherit it, so at every kernel boundary the
                 # compute kernels' CTAs are placed before pending CTAs of the (default-priority) gradient
-                # reduce-scatter kernels, which then only use what backward leaves free
+                # reduce-scatter / update kernels, which then only use what forward and backward leave free
                 hp = torch.cuda.Stream(device=self.device, priority=-1)
                 with torch.cuda.graph(self._graph, stream=hp):
-                    self._static_out = self._device_step([(self._static_sample, stats, False)], host_stats,
-                                                         device_stats_sync=False)
+                    self._static_out, _ = self._device_step([(self._static_sample, stats, False)], host_stats,
+                                                            static_weight=True)
             finally:
                 self._capturing = False
             # the captured update was only recorded, not executed: fall through to a replay
@@ -488,7 +534,7 @@ class Controller(object):
         self._graph.replay()
         # host-side Python state that _device_step normally leaves behind
         self.optimizer._skip = self._static_out[7] != 0
-        return self._static_out
+        return self._static_out, False
 
     def valid_step(self, sample):
         """Forward only (the reference never validates: train.py:93; available via --enable-validation)."""
@@ -496,6 +542,7 @@ class Controller(object):
         if prepared is None:
             return None
         sample_dev, _ = prepared
+        self.dp.flush()
         loss, sample_size, logging_output = self.task.valid_step(sample_dev, self._model)
         return float(loss), sample_size, logging_output
 

@@ -61,7 +61,7 @@ class BertH5pyData(torch.utils.data.Dataset):
         self.max_pred_length = max_pred_length
         self.path = path
         self._arrays = None          # loaded lazily, once per process (fork-safe for workers)
-        self._len, self._seq_len = self._probe()
+        self._len, self._seq_len, self._pred_width = self._probe()
 
     def _open(self):
         if self.path.endswith('.npz'):
@@ -77,12 +77,19 @@ class BertH5pyData(torch.utils.data.Dataset):
 
     def _probe(self):
         if self.path.endswith('.npz'):
-            arr = np.load(self.path)['input_ids']
-            return int(arr.shape[0]), int(arr.shape[1])
+            z = np.load(self.path)
+            arr = z['input_ids']
+            return int(arr.shape[0]), int(arr.shape[1]), int(z['masked_lm_positions'].shape[1])
         import h5py
         with h5py.File(self.path, 'r', libver='latest', swmr=True) as f:
             shp = f[self.keys[0]].shape
-            return int(shp[0]), int(shp[1])
+            return int(shp[0]), int(shp[1]), int(f['masked_lm_positions'].shape[1])
+
+    @property
+    def max_predictions(self) -> int:
+        """Most labelled positions a sample of this shard can carry (width of ``masked_lm_positions``, capped by
+        ``--max_pred_length``): fixes the capacity of the MLM row index before the first batch is seen."""
+        return min(self._pred_width, self.max_pred_length)
 
     @property
     def arrays(self):
@@ -177,6 +184,10 @@ class SyntheticBertData(torch.utils.data.Dataset):
     def size(self, idx: int):
         return self.seq_len
 
+    @property
+    def max_predictions_per_sample(self) -> int:
+        return min(self.max_predictions, self.max_pred_length)
+
     def set_epoch(self, epoch):
         pass
 
@@ -213,6 +224,14 @@ class ConBertH5pyData(torch.utils.data.Dataset):
 
     def __len__(self):
         return self.cumulative_sizes[-1]
+
+    @property
+    def max_predictions(self) -> int:
+        """Largest number of labelled positions any sample can carry (0 when the shards do not say)."""
+        out = 0
+        for d in self.datasets:
+            out = max(out, int(getattr(d, 'max_predictions_per_sample', getattr(d, 'max_predictions', 0)) or 0))
+        return out
 
     def _get_dataset_and_sample_index(self, idx: int):
         dataset_idx = bisect.bisect_right(self.cumulative_sizes, idx)

@@ -164,13 +164,15 @@ class EpochBatchIterator(object):
 
 
 class GroupedIterator(object):
-    """Chunks of ``chunk_size`` consecutive items (one chunk = one optimizer update)."""
+    """One optimizer update at a time: lists of up to ``chunk_size`` consecutive micro-batches (the last list of
+    an epoch may be shorter). ``offset`` is the number of updates already consumed when the wrapped iterator was
+    fast-forwarded on resume (data/iterators.py:214-241 of the reference)."""
 
     def __init__(self, iterable, chunk_size):
-        self._len = int(math.ceil(len(iterable) / float(chunk_size)))
-        self.offset = int(math.ceil(getattr(iterable, 'count', 0) / float(chunk_size)))
-        self.itr = iterable
-        self.chunk_size = chunk_size
+        self.chunk_size = max(1, int(chunk_size))
+        self.itr = iter(iterable)
+        self._len = -(-len(iterable) // self.chunk_size)
+        self.offset = -(-int(getattr(iterable, 'count', 0)) // self.chunk_size)
 
     def __len__(self):
         return self._len
@@ -179,38 +181,45 @@ class GroupedIterator(object):
         return self
 
     def __next__(self):
-        chunk = []
-        try:
-            for _ in range(self.chunk_size):
-                chunk.append(next(self.itr))
-        except StopIteration as e:
-            if len(chunk) == 0:
-                raise e
+        chunk = list(itertools.islice(self.itr, self.chunk_size))
+        if not chunk:
+            raise StopIteration
         return chunk
 
 
 class ShardedIterator(object):
-    """Every ``num_shards``-th element starting at ``shard_id``, padded to ceil(N / num_shards)."""
+    """Shard ``shard_id`` of ``num_shards``: items shard_id, shard_id + num_shards, ... of a sized iterable,
+    followed by ``fill_value`` until every shard has ceil(N / num_shards) items, so all ranks take the same
+    number of steps (data/iterators.py:244-275 of the reference). Positions come from the same index plan as
+    ``EpochBatchIterator`` (``data_utils.shard_plan``): -1 marks a padding slot."""
 
     def __init__(self, iterable, num_shards, shard_id, fill_value=None):
-        if shard_id < 0 or shard_id >= num_shards:
+        if not 0 <= shard_id < num_shards:
             raise ValueError('shard_id must be between 0 and num_shards')
-        self._sharded_len = len(iterable) // num_shards
-        if len(iterable) % num_shards > 0:
-            self._sharded_len += 1
-        self.itr = itertools.zip_longest(
-            range(self._sharded_len),
-            itertools.islice(iterable, shard_id, len(iterable), num_shards),
-            fillvalue=fill_value)
+        n = len(iterable)
+        self._plan = data_utils.shard_plan(None, n, num_shards, shard_id)
+        self._fill = fill_value
+        self._src = iter(iterable)
+        self._cursor = 0      # items of the source consumed so far
+        self._i = 0           # position in the plan
 
     def __len__(self):
-        return self._sharded_len
+        return len(self._plan)
 
     def __iter__(self):
         return self
 
     def __next__(self):
-        return next(self.itr)[1]
+        if self._i >= len(self._plan):
+            raise StopIteration
+        want = int(self._plan[self._i])
+        self._i += 1
+        if want < 0:
+            return self._fill
+        skip = want - self._cursor
+        item = next(itertools.islice(self._src, skip, skip + 1))
+        self._cursor = want + 1
+        return item
 
 
 class PrefetchIterator(object):

@@ -360,8 +360,14 @@ class BertPreTrainedModel(nn.Module):
 
     def init_bert_weights(self, module):
         """Linear / Embedding / LinearActivation weights ~ N(0, initializer_range); LayerNorm (1, 0);
-        biases 0 (bert_modeling.py:599-610; there LinearActivation keeps its kaiming init because it is
-        not an nn.Linear -- normal init for it too is the evident intent)."""
+        biases 0 (bert_modeling.py:599-610). In the reference ``LinearActivation`` (FFN1, pooler, MLM
+        transform) is not an ``nn.Linear``, so those layers silently keep their constructor's kaiming-uniform
+        weights and uniform biases; normal init for them too is the evident intent and the default here.
+        ``config.linear_activation_init = 'reference'`` (``--init-linear-activation reference``) reproduces the
+        reference's from-scratch initialisation exactly."""
+        like_reference = getattr(self.config, 'linear_activation_init', 'normal') == 'reference'
+        if isinstance(module, LinearActivation) and like_reference:
+            return
         if isinstance(module, (nn.Linear, nn.Embedding, LinearActivation)):
             module.weight.data.normal_(mean=0.0, std=self.config.initializer_range)
         elif isinstance(module, BertLayerNorm):

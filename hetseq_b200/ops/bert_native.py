@@ -404,17 +404,20 @@ class LinearXentFn(torch.autograd.Function):
         ld = (V + 127) // 128 * 128 if V > 128 else 8
         logits = torch.empty(M, ld, dtype=x.dtype, device=x.device)
         native.gemm(x, weight, logits, M, V, K, lda=K, ldb=K, ldc=ld, bias=bias)
-        loss = torch.zeros(1, dtype=torch.float32, device=x.device)
-        native.xent(logits, ld, labels, M, V, loss, False, write_grad=True)
-        ctx.save_for_backward(x, weight, logits)
+        # [loss, 1 / number of labelled rows]: the stored gradient is softmax - onehot, O(1) entries that
+        # survive fp16; the 1/n (and the upstream gradient with the loss scale) go into the GEMMs' fp32 alpha
+        out2 = torch.zeros(2, dtype=torch.float32, device=x.device)
+        loss = out2[:1]
+        native.xent(logits, ld, labels, M, V, loss, False, write_grad=True, inv_count_out=out2[1:])
+        ctx.save_for_backward(x, weight, logits, out2)
         ctx.meta = (wparams, bparams, M, K, V, ld)
         return loss[0]
 
     @staticmethod
     def backward(ctx, g):
-        x, weight, dlogits = ctx.saved_tensors
+        x, weight, dlogits, out2 = ctx.saved_tensors
         wparams, bparams, M, K, V, ld = ctx.meta
-        g = g.to(torch.float32).reshape(1).contiguous()
+        g = (g.to(torch.float32).reshape(1) * out2[1:]).contiguous()
         dx = torch.empty(M, K, dtype=x.dtype, device=x.device)
         native.gemm(dlogits, weight, dx, M, K, V, lda=ld, ldb=K, ldc=K, b_mn=True, alpha_dev=g)
         wg, acc = _wgrad_target(wparams)
@@ -470,6 +473,12 @@ class NativeBert(object):
                 self.sites[(id(layer), tag)] = rng.new_site()
         self.site_emb = rng.new_site()
         self.bert.native = self
+        # Parameters may still be arriving from the peers while the forward pass runs (the fused data-parallel
+        # backend overlaps its all-gather with it, parallel/fused_dp.py): every block waits for its own slice of
+        # the flat buffer right before its first kernel. The lists are in flat order, so each gate is monotone.
+        self.gate_params = {id(layer): list(layer.parameters()) for layer in self.bert.encoder.layer}
+        self.gate_params['emb'] = list(self.bert.embeddings.parameters())
+        buffer.gated_forward = True
         if hasattr(model, 'cls') and hasattr(model, 'bert') and model.__class__.__name__ == 'BertForPreTraining':
             model.native = self
             # the tied decoder / word-embedding matrix gets two gradient contributions per backward
@@ -493,6 +502,7 @@ class NativeBert(object):
         """x: [B, S, H] (or [M, H] with self._bs set); add_mask: [B, S] additive fp32 mask."""
         B, S = self._bs
         H = self.H
+        self.buffer.gate(self.gate_params[id(layer)])
         x2 = x.reshape(B * S, H)
         training = layer.training
         qkv_w, qkv_b, ws, bs = self.packed[id(layer)]
@@ -524,6 +534,7 @@ class NativeBert(object):
         emb = bert.embeddings
         ids = input_ids.reshape(-1).contiguous()
         seg = token_type_ids.reshape(-1).to(ids.dtype).contiguous()
+        self.buffer.gate(self.gate_params['emb'])
         z = EmbeddingSumFn.apply(emb.word_embeddings.weight, emb.position_embeddings.weight,
                                  emb.token_type_embeddings.weight, ids, seg, emb.word_embeddings.weight,
                                  emb.position_embeddings.weight, emb.token_type_embeddings.weight, B, S)
@@ -534,6 +545,8 @@ class NativeBert(object):
                               checkpoint_activations=checkpoint_activations)
         seq = layers[-1]
         pool = bert.pooler.dense_act
+        if self.buffer.param_gate is not None:
+            self.buffer.param_gate(self.buffer.total)    # pooler + whatever head follows: everything must be in
         # pooler reads the CLS rows in place: row stride S*H, no gather copy
         pooled = linear(seq.view(B * S, self.H)[::S], pool.weight, pool.bias, [pool.weight], [pool.bias], act=ACT_TANH,
                         ldx=S * self.H)

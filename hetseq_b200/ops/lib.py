@@ -64,6 +64,7 @@ def load() -> ctypes.CDLL:
     lib.hs_colsum_scratch_elems.argtypes = [ctypes.c_int, ctypes.c_int]
     lib.hs_attention_supported.argtypes = [ctypes.c_int, ctypes.c_int]
     lib.hs_dp_signal_words.argtypes = [ctypes.c_int, ctypes.c_int]
+    lib.hs_dp_max_gather_buckets.restype = ctypes.c_int
     _declare(lib)
     _lib = lib
     return lib

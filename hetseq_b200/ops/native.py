@@ -91,13 +91,14 @@ def colsum(x, M, N, ld, out, accumulate):
     return out
 
 
-def xent(logits, ld, labels, rows, V, loss, accumulate_loss, write_grad=True):
-    """In-place: logits become d(loss)/d(logits); returns per-row losses."""
+def xent(logits, ld, labels, rows, V, loss, accumulate_loss, write_grad=True, inv_count_out=None):
+    """In-place: logits become d(loss)/d(logits); returns per-row losses. With ``inv_count_out`` (1-element fp32
+    tensor) the stored gradient is softmax - onehot without the 1/n_valid, which lands in ``inv_count_out``."""
     L = lib.load()
     row_loss = torch.empty(rows, dtype=torch.float32, device=logits.device)
     lib.check(L.hs_xent(logits.data_ptr(), ld, labels.data_ptr(), int(labels.dtype == torch.int64), rows, V,
                         row_loss.data_ptr(), lib.ptr(loss), int(accumulate_loss), int(write_grad),
-                        lib.dtype_code(logits.dtype), lib.stream_ptr()), 'hs_xent')
+                        lib.ptr(inv_count_out), lib.dtype_code(logits.dtype), lib.stream_ptr()), 'hs_xent')
     return row_loss
 
 

@@ -22,6 +22,16 @@ def set_step_seed(seed: int, rank: int = 0) -> None:
         t.copy_(torch.tensor(_host, dtype=torch.int64), non_blocking=True)
 
 
+def set_micro_batch(index: int) -> None:
+    """Fold the micro-batch number of the current update into the seed (``--update-freq`` > 1): the masks are a
+    pure function of (seed, site, element), so without this every micro-batch of an update would draw the very
+    same masks, whereas the reference draws fresh ones from the torch generator for each (controller.py:235).
+    Forward and backward of one micro-batch run between two calls, so recomputation stays consistent."""
+    base = _host[0]
+    for t in _dev.values():
+        t.copy_(torch.tensor([base + 2654435761 * int(index), _host[1]], dtype=torch.int64), non_blocking=True)
+
+
 def seed_tensor(device) -> torch.Tensor:
     device = torch.device(device)
     key = (device.type, device.index)

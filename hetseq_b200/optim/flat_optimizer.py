@@ -64,6 +64,8 @@ class _Optimizer(object):
 
     #: names of the fp32 state buffers, in checkpoint order
     state_names = ()
+    #: which update rule the native kernels run ('adam' | 'adadelta')
+    kind = ''
 
     def __init__(self, args, params, dp=None):
         super().__init__()
@@ -100,11 +102,16 @@ class _Optimizer(object):
         #   scale_t  = [loss scale]           hyper_t = [lr, sqrt(1-b2^t)/(1-b1^t)]
         self.scale_t = torch.full((1,), self.loss_scale, dtype=torch.float32, device=dev)
         self.hyper_t = torch.zeros(2, dtype=torch.float32, device=dev)
+        #: what hyper_t held during the previous update: the fused backend applies update n while step n+1 runs
+        self.hyper_prev_t = torch.zeros(2, dtype=torch.float32, device=dev)
+        self._ss_dev = None       # this rank's sample size (device scalar) for the in-kernel gradient denominator
         self._host_scalars = torch.zeros(3, dtype=torch.float32)
         if dev.type == 'cuda':
             self._host_scalars = self._host_scalars.pin_memory()
         self._native = None
         self._init_native()
+        if getattr(dp, 'fused', False):
+            dp.bind_optimizer(self)
 
     # -- configuration --------------------------------------------------------------------------
     @property
@@ -152,6 +159,7 @@ class _Optimizer(object):
         of every update (zero_grad). When the update is replayed from a CUDA graph the copies are part of
         the graph and only ``write_host_scalars`` runs on the host before each replay."""
         self.write_host_scalars()
+        self.hyper_prev_t.copy_(self.hyper_t)
         self.hyper_t.copy_(self._host_scalars[:2], non_blocking=True)
         self.scale_t.copy_(self._host_scalars[2:3], non_blocking=True)
 
@@ -171,7 +179,14 @@ class _Optimizer(object):
         if self.scaler is not None:
             self._scaled = True
             loss = loss * self.scale_t[0]
+        self.buffer.begin_backward()
         loss.backward()
+
+    def set_grad_denominator(self, sample_size):
+        """This rank's sample size as a device scalar. The fused backend sums it over ranks inside the norm
+        exchange and divides the summed gradients by it (controller.py:338-339 without a collective or a host
+        read); the other backends get an explicit ``multiply_grads(world / sample_size)`` instead."""
+        self._ss_dev = sample_size
 
     def multiply_grads(self, c):
         """Multiply gradients by ``c`` (float or 0-dim tensor) -- deferred into the update."""
@@ -214,7 +229,7 @@ class _Optimizer(object):
             # every rank the same norm / clip coefficient / overflow flag
             md = self._pending_mult()
             norm = self.dp.norm_exchange(1.0 if torch.is_tensor(md) else float(md), md if torch.is_tensor(md) else None,
-                                         float(max_norm))
+                                         float(max_norm), sample_size=self._ss_dev)
             self._skip = self.dp.scalars[2] != 0
             self._fused_ready = True
             return norm
@@ -236,6 +251,7 @@ class _Optimizer(object):
         self._mult, self._mult_dev, self._skip = 1.0, None, None
         self._fused_ready = False
         self._scaled = False
+        self._ss_dev = None
 
     # -- update ---------------------------------------------------------------------------------
     def step(self, closure=None):
@@ -255,7 +271,7 @@ class _Optimizer(object):
         if self._skip is None or (fused and not getattr(self, '_fused_ready', False)):
             self.clip_grad_norm(0.0)
         if fused:
-            self.dp.adam_allgather(self, 1.0, hyper_dev=self.hyper_t)
+            self.dp.queue_update(self)      # applied next to the next forward pass (or by dp.flush())
         elif self._native is not None:
             self._native.update(self._pending_mult(), self._skip if self.scaler is not None else None,
                                 hyper_dev=self.hyper_t)
@@ -361,6 +377,7 @@ class _Adam(_Optimizer):
     """fairseq Adam (AdamW-style decoupled decay, bias correction) -- math of optim.py:162-231."""
 
     state_names = ('exp_avg', 'exp_avg_sq')
+    kind = 'adam'
 
     @staticmethod
     def add_args(parser):
@@ -396,6 +413,7 @@ class _Adadelta(_Optimizer):
     """Adadelta with coupled L2 decay -- math of optim.py:263-304."""
 
     state_names = ('square_avg', 'acc_delta')
+    kind = 'adadelta'
 
     @staticmethod
     def add_args(parser):

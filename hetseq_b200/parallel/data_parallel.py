@@ -56,6 +56,10 @@ class LocalBackend(object):
     def check_params_consistent(self) -> bool:
         return True
 
+    def flush(self, sync: bool = True):
+        """Make every queued parameter update visible in ``flat_param`` (only the fused backend defers any)."""
+        pass
+
     def close(self):
         pass
 

@@ -77,6 +77,8 @@ class FlatParamBuffer(object):
         self.shard_size = self.total // self.world_size
         self.num_blocks = self.total // (self.world_size * CHUNK)
 
+        #: where the two flat buffers came from (a SymmetricPool under the fused NVLink backend, else None)
+        self.allocator = allocator
         alloc = allocator or (lambda n, dt, dev: torch.zeros(n, dtype=dt, device=dev))
         self.flat_param = alloc(self.total, self.param_dtype, self.device)
         self.flat_grad = alloc(self.total, self.grad_dtype, self.device)
@@ -102,6 +104,14 @@ class FlatParamBuffer(object):
         self._notifications: List[int] = [0] * len(self.params)
         self._is_small = [p.numel() <= SMALL_PARAM_NUMEL for p in self.params]
         self._small_grads = [g for g, sm in zip(self.main_grads, self._is_small) if sm]
+        #: hooks of a backend whose parameter update overlaps the next forward pass (parallel/fused_dp.py):
+        #: ``param_gate(flat_end)`` is called by a gated forward pass in front of the first kernel that reads
+        #: parameters below flat offset ``flat_end``; ``before_backward()`` once before gradients are written
+        self.param_gate: Optional[Callable[[int], None]] = None
+        self.before_backward: Optional[Callable[[], None]] = None
+        #: set by models whose forward calls ``gate`` (ops/bert_native.py); others get everything up front
+        self.gated_forward = False
+        self._small_zero_pending = False
         self.zero_grad()
 
     # -- gradient plumbing ----------------------------------------------------------------------
@@ -141,6 +151,27 @@ class FlatParamBuffer(object):
         for i in range(len(self._notifications)):
             self._notifications[i] = 0
 
+    def gate(self, params) -> None:
+        """Forward-side wait for the (asynchronously arriving) parameters ``params`` and everything before them
+        in the flat buffer. A no-op unless a backend installed ``param_gate``."""
+        if self.param_gate is None:
+            return
+        end = 0
+        for p in params:
+            i = p._hs_flat[1]
+            end = max(end, self.offsets[i] + self.numels[i])
+        self.param_gate(end)
+
+    def begin_backward(self) -> None:
+        """Called once per micro-batch right before ``loss.backward()``: lets the backend finish reading the
+        previous update's gradients, then clears the small (atomically accumulated) gradients if this is the
+        first backward pass of the accumulation window."""
+        if self.before_backward is not None:
+            self.before_backward()
+        if self._small_zero_pending:
+            self._small_zero_pending = False
+            torch._foreach_zero_(self._small_grads)
+
     def grad_target(self, p: torch.nn.Parameter) -> Tuple[torch.Tensor, bool]:
         """(main_grad view, accumulate?) for an op that writes the gradient itself."""
         i = p._hs_flat[1]
@@ -173,8 +204,13 @@ class FlatParamBuffer(object):
             self.flat_grad.zero_()
         elif self._small_grads:
             # small parameters (biases, LayerNorm) are produced by kernels that accumulate with atomics; one
-            # multi-tensor fill here is cheaper than a memset node in front of each of those kernels
-            torch._foreach_zero_(self._small_grads)
+            # multi-tensor fill is cheaper than a memset node in front of each of those kernels. With a backend
+            # whose update still reads the previous gradients during the forward pass the fill waits until
+            # ``begin_backward``.
+            if self.before_backward is not None:
+                self._small_zero_pending = True
+            else:
+                torch._foreach_zero_(self._small_grads)
         for i, p in enumerate(self.params):
             # after a memset every view is a valid partial sum, so later writes must accumulate
             self._written[i] = bool(set_to_zero) or self._is_small[i]
@@ -183,6 +219,8 @@ class FlatParamBuffer(object):
     def finalize_grads(self) -> None:
         """End of the accumulation window: parameters that received no gradient at all (unused in this
         update) get zeros instead of the previous window's values, and are reported ready."""
+        if self._small_zero_pending:       # an update without any backward pass
+            self.begin_backward()
         for i, w in enumerate(self._written):
             if not w:
                 self.main_grads[i].zero_()

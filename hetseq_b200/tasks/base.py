@@ -108,9 +108,11 @@ class Task(object):
         from hetseq_b200.utils import utils
         return utils.move_to_device(sample, device)
 
-    def train_step(self, sample, model, optimizer, ignore_grad=False, stats=None):
+    def train_step(self, sample, model, optimizer, ignore_grad=False, stats=None, weight=None):
         """forward + backward on one micro-batch (tasks.py:139-177). Returns
-        (loss, sample_size, logging_output); ``loss`` stays on the device (no sync)."""
+        (loss, sample_size, logging_output); ``loss`` stays on the device (no sync). ``weight`` (device
+        scalar) replaces the host-side weighting below: a captured CUDA graph reads the batch weight -- the
+        number of real sentences, 0 for a padding batch -- from device memory on every replay."""
         model.train()
         loss = model(*sample)
         if ignore_grad:
@@ -127,7 +129,9 @@ class Task(object):
         # 'batch' mode: the model returns a batch mean; weight it by the batch size so that dividing
         # the accumulated gradient by the global sample_size yields the true mean over sentences.
         # 'reference' mode: back-propagate the mean itself, as tasks.py:176 does.
-        if getattr(self.args, 'sample_size_mode', 'batch') == 'batch' and nsentences != 1:
+        if weight is not None:
+            optimizer.backward(loss * weight)
+        elif getattr(self.args, 'sample_size_mode', 'batch') == 'batch' and nsentences != 1:
             optimizer.backward(loss * float(nsentences))
         else:
             optimizer.backward(loss)

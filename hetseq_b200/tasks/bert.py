@@ -27,6 +27,10 @@ class LanguageModelingTask(Task):
     def __init__(self, args, dictionary=None):
         super().__init__(args)
         self.dictionary = dictionary
+        #: most labelled positions per sequence seen / announced by the shards: capacity of the MLM row index
+        self._max_pred_seen = 0
+        #: rows every device batch is padded to (set by the Controller under --cuda-graph: static shapes)
+        self.static_batch_size = 0
 
     @staticmethod
     def add_args(parser):
@@ -46,6 +50,11 @@ class LanguageModelingTask(Task):
         parser.add_argument('--checkpoint-activations', action='store_true',
                             help='recompute encoder activations in backward in chunks of ceil(sqrt(L)) layers '
                                  '(the reference has the code but never enables it: bert_modeling.py:470-476)')
+        parser.add_argument('--init-linear-activation', default='normal', choices=['normal', 'reference'],
+                            help="initial weights of the bias+activation Linear layers (FFN1, pooler, MLM transform): "
+                                 "'normal' = N(0, initializer_range) like every other Linear; 'reference' = left at "
+                                 "the constructor's kaiming-uniform, which is what the reference's init_bert_weights "
+                                 "does (bert_modeling.py:599-610) -- use it to compare from-scratch loss curves")
         parser.add_argument('--mlm-all-positions', action='store_true',
                             help='run the MLM decoder + loss over all B*S positions like the reference '
                                  '(bert_modeling.py:878-882) instead of the labelled rows only')
@@ -58,6 +67,7 @@ class LanguageModelingTask(Task):
     def build_model(self, args):
         from hetseq_b200.models.bert import BertConfig, BertForPreTraining
         config = BertConfig.from_json_file(args.config_file)
+        config.linear_activation_init = getattr(args, 'init_linear_activation', 'normal')
         return BertForPreTraining(config, args=args)
 
     def load_dataset(self, split, **kwargs):
@@ -70,6 +80,7 @@ class LanguageModelingTask(Task):
                                    seed=args.seed + (0 if split == args.train_subset else 1),
                                    max_pred_length=args.max_pred_length)
             self.datasets[split] = ConBertH5pyData([ds])
+            self._max_pred_seen = max(self._max_pred_seen, self.datasets[split].max_predictions)
             print('| synthetic {} sentences for split {}'.format(len(ds), split), flush=True)
             return
         path = args.data
@@ -84,13 +95,32 @@ class LanguageModelingTask(Task):
         dataset = ConBertH5pyData(datasets)
         print('| loaded {} sentences from: {}'.format(len(dataset), path), flush=True)
         self.datasets[split] = dataset
+        # every rank derives the same MLM capacity from the shards themselves, before the first batch
+        self._max_pred_seen = max(self._max_pred_seen, dataset.max_predictions)
         print('| loading finished')
 
     def sample_stats(self, sample):
-        # real tokens = attended positions (input_mask is sample[2]); computed on the host copy
+        # real tokens = attended positions (input_mask is sample[2]); computed on the host copy. Rows added by
+        # pad_batch attend to nothing and are not counted as sentences.
         input_ids, mask = sample[0], sample[2]
-        ntokens = int(mask.sum()) if mask.device.type == 'cpu' else int(input_ids.numel())
-        return int(input_ids.shape[0]), ntokens
+        if mask.device.type != 'cpu':
+            return int(input_ids.shape[0]), int(input_ids.numel())
+        return int((mask.sum(dim=1) > 0).sum()), int(mask.sum())
+
+    def pad_batch(self, sample, rows: int):
+        """Grow a collated host batch to ``rows`` sequences with inert ones: no attended token, every MLM label
+        and the NSP label at the ignore index (-1), so they add nothing to either loss (both are means over the
+        non-ignored rows, bert_modeling.py:881-886) or to any gradient. Keeps the shapes of a short last batch
+        equal to those of a full one (static shapes for the captured CUDA graph)."""
+        B = int(sample[0].shape[0])
+        if rows <= B or len(sample) != 5:
+            return sample
+        pad = rows - B
+        out = []
+        for k, t in enumerate(sample):
+            fill = -1 if k >= 3 else 0
+            out.append(torch.cat([t, torch.full((pad,) + tuple(t.shape[1:]), fill, dtype=t.dtype)], dim=0))
+        return out
 
     def mlm_index(self, masked_lm_labels: torch.Tensor):
         """Host-side (numpy) flat indices + labels of the labelled positions, padded with -1 to a fixed
@@ -100,7 +130,9 @@ class LanguageModelingTask(Task):
         rows = np.nonzero(lab != -1)[0]
         B = masked_lm_labels.shape[0]
         per_seq = int((masked_lm_labels != -1).sum(1).max()) if rows.size else 1
-        self._max_pred_seen = max(getattr(self, '_max_pred_seen', 0), per_seq,
+        # normally fixed up front by load_dataset (the shards announce their width); only a hand-made batch with
+        # more labels than that can still grow it
+        self._max_pred_seen = max(self._max_pred_seen, per_seq,
                                   int(getattr(self.args, 'synthetic_max_predictions', 0) or 0)
                                   if getattr(self.args, 'synthetic_data', False) else 0)
         cap = (max(B * self._max_pred_seen, rows.size, 1) + 63) // 64 * 64
@@ -126,6 +158,8 @@ class LanguageModelingTask(Task):
         if isinstance(sample, utils.PackedSample):
             return sample                    # already prepared by host_prepare()
         sample = list(sample)
+        if self.static_batch_size and len(sample) == 5 and sample[0].device.type == 'cpu':
+            sample = self.pad_batch(sample, self.static_batch_size)
         if len(sample) == 5 and sample[3].device.type == 'cpu' and not getattr(self.args, 'mlm_all_positions', False):
             sample += list(self.mlm_index(sample[3]))
         if narrow:

@@ -99,6 +99,11 @@ def save_checkpoint(args, controller, epoch_itr, val_loss):
         if not at_end:
             prune(args.save_dir, UPDATES_PATTERN, args.keep_interval_updates)
         prune(args.save_dir, EPOCH_PATTERN, args.keep_last_epochs)
+    if names and distributed_utils.get_world_size() > 1:
+        # Only the master writes and copies (possibly for many seconds, to slow storage). Hold the other ranks
+        # here instead of letting them queue kernels that spin on the master's flags: a host-side barrier is
+        # bounded by the process-group timeout (--distributed-timeout), like every wait of the reference.
+        distributed_utils.barrier()
 
 
 def load_checkpoint(args, controller):

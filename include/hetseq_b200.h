@@ -153,9 +153,12 @@ HS_API int hs_colsum_scratch_elems(int M, int N);
 /* CrossEntropyLoss(ignore_index=-1), mean reduction (bert_modeling.py:881-886, K13). Per row: online
  * log-sum-exp, row_loss[r]; with write_grad the logits are overwritten in place by
  * (softmax - onehot) / n_valid (ignored rows and pad columns [V, ld) become 0). loss (optional)
- * (= or +=) mean over valid rows. labels int32 or int64. */
+ * (= or +=) mean over valid rows. labels int32 or int64. With inv_count_out non-NULL the stored gradient is
+ * softmax - onehot WITHOUT the 1/n_valid (O(1) values survive fp16; ~1e-7 ones do not) and *inv_count_out
+ * receives 1/n_valid for the consumer to fold into its GEMM alpha. */
 HS_API int hs_xent(void* logits, int ld, const void* labels, int label_is_i64, int rows, int V, float* row_loss,
-                   float* loss, int accumulate_loss, int write_grad, int dtype, hs_stream_t stream);
+                   float* loss, int accumulate_loss, int write_grad, float* inv_count_out, int dtype,
+                   hs_stream_t stream);
 /* dst[r,:] = src[idx[r],:] (idx < 0 -> zeros): only the labelled positions enter the MLM head (Q21/W9). */
 HS_API int hs_gather_rows(const void* src, const void* idx, int idx_is_i64, void* dst, int rows, int row_bytes,
                           hs_stream_t stream);
@@ -191,42 +194,72 @@ HS_API int hs_attention_bwd(const void* qkv, const float* mask, const void* ctx,
                             void* dqkv, float* dbias, int accumulate_bias, int B, int S, int heads, int H,
                             float dropout_p, const long long* seed, unsigned site, int dtype, hs_stream_t stream);
 
-/* ---- fused data-parallel gradient path over NVLink peer memory (csrc/comm_sm100.cu) ------------------- */
+/* ---- fused data-parallel gradient path over NVLink / NVSwitch (csrc/comm_sm100.cu) ---------------------- */
 /* Replaces DDP's bucketed NCCL all-reduce (controller.py:78-86, N4) + multiply_grads + clip_grad_norm +
- * Adam.step on every rank (optim.py:59-70,162-231, K15-K17) -- SURVEY.md W1. W <= 16 ranks of one node.
- * Buffers come from hs_ipc_alloc and are mapped into every peer with hs_ipc_open; *_ptrs are HOST arrays
- * of W device pointers indexed by rank (entry [rank] is the local buffer). Ownership is cyclic by chunk:
- * chunk c of the flat buffers belongs to rank c % W. Flags in the signal pads carry `epoch` (the update
- * number, strictly increasing); when `epoch_dev` is non-NULL the kernels read the epoch from that device
- * word instead (so a captured CUDA graph stays valid across updates). Pads are hs_dp_signal_words()
+ * Adam.step / Adadelta.step on every rank (optim.py:59-70,162-231,263-304, K15-K18) -- SURVEY.md W1, W12.
+ * W <= 16 ranks of one node. The flat gradient / parameter buffers and one signal pad per rank live in
+ * symmetric memory: *_ptrs are HOST arrays of W device pointers indexed by rank (entry [rank] is the local
+ * buffer, the others are peer mappings); *_mc is the NVLS multicast address of the same buffer, or NULL --
+ * then the kernels use peer loads / stores instead of multimem.ld_reduce / multimem.st. Ownership is
+ * cyclic by chunk: chunk c of the flat buffers belongs to rank c % W. Flags in the signal pads carry `epoch`
+ * (the update number, strictly increasing); when `epoch_dev` is non-NULL the kernels read the epoch from that
+ * device word instead (so a captured CUDA graph stays valid across updates). Pads are hs_dp_signal_words()
  * 32-bit words, zero-initialised. */
-HS_API int hs_ipc_alloc(size_t bytes, void** ptr, unsigned char* handle64);
+HS_API int hs_ipc_alloc(size_t bytes, void** ptr, unsigned char* handle64);   /* cudaMalloc + CUDA IPC handle */
 HS_API int hs_ipc_open(const unsigned char* handle64, void** ptr);
 HS_API int hs_ipc_close(void* ptr);
 HS_API int hs_ipc_free(void* ptr);
 HS_API int hs_dp_signal_words(int W, int max_buckets);
+HS_API int hs_dp_max_gather_buckets(void);
+/* Upper bound of every in-kernel wait on a peer, for the current device (default 1800 s, the process-group
+ * timeout that bounds the reference's waits inside NCCL). Beyond it the kernel prints which peer it was
+ * waiting for and traps. Synchronous: call it at set-up. */
+HS_API int hs_dp_set_timeout(double seconds);
 /* One bucket = chunks [chunk_begin, chunk_end). Announces the bucket to all peers, waits for theirs, then
- * sums the W copies of every owned chunk straight from peer memory into the local fp32 gradient and adds
- * the squared sum into *sumsq_accum. Launch on a side stream as soon as the bucket's gradients are final. */
-HS_API int hs_dp_reduce_scatter(void* const* grad_ptrs, void* const* sig_ptrs, int rank, int W,
+ * reduces the W copies of every owned chunk into the local fp32 gradient and adds the squared sum into
+ * *sumsq_accum. Launch on a side stream as soon as the bucket's gradients are final. */
+HS_API int hs_dp_reduce_scatter(void* const* grad_ptrs, const void* grads_mc, void* const* sig_ptrs, int rank, int W,
                                 long long chunk_begin, long long chunk_end, int chunk, int slot, unsigned epoch,
                                 const unsigned* epoch_dev, float* sumsq_accum, int nblocks, hs_stream_t stream);
-/* All ranks exchange their norm partial through the pads and derive identical
- * out4 = [grad_norm, multiplier * clip coefficient, overflow flag, global sum of squares]; *skip_out = flag. */
+/* All ranks exchange their norm partial and their sample size through the pads and derive identical
+ * out5 = [grad_norm, multiplier, overflow flag, global sum of squares, global sample size]; *skip_out = flag.
+ * multiplier = mult_host * (*mult_dev) * clip coefficient, and additionally / (sum of sample sizes) when
+ * `sample_size` is non-NULL (the reference's multiply_grads(world / sample_size) on DDP's mean,
+ * controller.py:338-339). `pending` (optional) is set to 1: an update is waiting for hs_dp_update_allgather. */
 HS_API int hs_dp_norm_exchange(void* const* sig_ptrs, int rank, int W, unsigned epoch, const unsigned* epoch_dev,
-                               float* sumsq_accum, float mult_host, const float* mult_dev, float max_norm, float* out4, int* skip_out,
-                               hs_stream_t stream);
-/* Adam (math of optim.py:162-231) on the owned chunks; the updated 16-bit parameters are stored into all W
- * parameter buffers (the all-gather). scalars = out4 of hs_dp_norm_exchange. */
-HS_API int hs_dp_adam_allgather(const float* grad, float* master, float* exp_avg, float* exp_avg_sq,
-                                void* const* param_ptrs, void* const* sig_ptrs, int rank, int W, long long nblocks,
-                                int chunk, int out_dtype, float lr, float beta1, float beta2, float eps,
-                                float weight_decay, float step_factor, const float* scalars, const float* hyper_dev,
-                                unsigned epoch, const unsigned* epoch_dev, unsigned int* done_counter, int grid_blocks,
-                                hs_stream_t stream);
-/* Returns (on the stream) once every rank's parameter stores of update `epoch` have landed locally. */
-HS_API int hs_dp_wait_params(void* const* sig_ptrs, int rank, int W, unsigned epoch, const unsigned* epoch_dev,
-                             hs_stream_t stream);
+                               float* sumsq_accum, float mult_host, const float* mult_dev, const float* sample_size,
+                               float max_norm, float* out5, int* skip_out, int* pending, hs_stream_t stream);
+/* opt = 0: Adam (optim.py:162-231; a_coef/b_coef = beta1/beta2, state1/2 = exp_avg/exp_avg_sq),
+ * opt = 1: Adadelta (optim.py:263-304; a_coef = rho, state1/2 = square_avg/acc_delta) on the owned chunks, in
+ * flat order; the updated 16-bit parameters are stored into all W parameter buffers (the all-gather).
+ * The buffer is cut into `ngather` slices ("gather buckets"); each is published to every peer with its own flag
+ * (value epoch + epoch_offset) as soon as this rank's part of it is stored. scalars = out5 of
+ * hs_dp_norm_exchange. With `pending` non-NULL the update is applied only if *pending != 0 (and *pending is
+ * cleared); the flags are published either way. counters: ngather + 1 zeroed words. */
+HS_API int hs_dp_update_allgather(int opt, const float* grad, float* master, float* state1, float* state2,
+                                  void* const* param_ptrs, void* params_mc, void* const* sig_ptrs, int rank, int W,
+                                  long long nblocks, int chunk, int out_dtype, float lr, float a_coef, float b_coef,
+                                  float eps, float weight_decay, float step_factor, const float* scalars,
+                                  const float* hyper_dev, unsigned epoch, const unsigned* epoch_dev, int epoch_offset,
+                                  unsigned int* counters, int* pending, int ngather, int grid_blocks,
+                                  hs_stream_t stream);
+/* Gather bucket that owned block `block` (of nblocks per rank) falls into. */
+HS_API int hs_dp_gather_bucket_of(long long nblocks, int ngather, long long block);
+/* Returns (on the stream) once gather buckets [j_lo, j_hi] of update `epoch + epoch_offset` have arrived from
+ * every rank. The forward pass queues one in front of the first kernel that reads a slice. */
+HS_API int hs_dp_wait_params(void* const* sig_ptrs, int rank, int W, int j_lo, int j_hi, unsigned epoch,
+                             const unsigned* epoch_dev, int epoch_offset, hs_stream_t stream);
+/* Protocol test on ONE GPU: W virtual ranks (blocks_per_rank CTAs each) run one whole update -- the same device
+ * code as the four kernels above, peer-load / peer-store variant -- inside one cooperative launch. All pointer
+ * arguments are host arrays of W device pointers (one "rank" each); barrier_words: W words. */
+HS_API int hs_dp_emulate_step(int W, int blocks_per_rank, void* const* grad_ptrs, void* const* param_ptrs,
+                              void* const* sig_ptrs, float* const* sumsq, const float* const* sample_size,
+                              float* const* scalars, int* const* skip, float* const* master, float* const* state1,
+                              float* const* state2, unsigned int* const* counters, int* const* pending,
+                              unsigned int* barrier_words, long long total_chunks, long long chunks_per_bucket,
+                              int chunk, int ngather, int opt, int out_dtype, float lr, float a_coef, float b_coef,
+                              float eps, float weight_decay, float step_factor, float mult_host, float max_norm,
+                              unsigned epoch, hs_stream_t stream);
 
 #ifdef __cplusplus
 }

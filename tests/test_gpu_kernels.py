@@ -226,6 +226,50 @@ def test_xent(nat, dt, V):
     assert torch.count_nonzero(logits[:, V:]) == 0
 
 
+def test_mlm_head_gradient_survives_fp16_at_init():
+    """640 labelled rows, V = 30522, near-uniform logits (a freshly initialised model): softmax / n_valid is ~5e-8,
+    far below the fp16 subnormal range. The head stores softmax - onehot and carries 1/n_valid (and the upstream
+    gradient) in the fp32 alpha of the decoder GEMMs; dx and dW must match an fp32 restatement of
+    /root/reference/bert_modeling.py:547,881-882."""
+    from hetseq_b200.ops import bert_native as bn
+    torch.manual_seed(11)
+    M, K, V = 640, 256, 30522
+    x = (torch.randn(M, K, device='cuda') * 0.5).half().requires_grad_(True)
+    w = (torch.randn(V, K, device='cuda') * 0.02).half()
+    b = torch.zeros(V, device='cuda').half()
+    labels = torch.randint(0, V, (M,), device='cuda', dtype=torch.int32)
+    labels[::7] = -1
+
+    class P(object):      # stands in for the flat buffer: LinearXentFn only needs a gradient target
+        pass
+    wg = torch.zeros(V, K, device='cuda')
+    bg = torch.zeros(V, device='cuda')
+    orig_target, orig_notify = bn._wgrad_target, bn._notify
+    bn._wgrad_target = lambda params: ((wg.view(-1), False) if params[0] == 'w' else (bg, False))
+    bn._notify = lambda params: None
+    try:
+        loss = bn.LinearXentFn.apply(x, w, b, labels, ['w'], ['b'])
+        (loss * 1024.0).backward()      # an upstream gradient like the loss scale
+    finally:
+        bn._wgrad_target, bn._notify = orig_target, orig_notify
+    xr = x.detach().float().requires_grad_(True)
+    wr = w.float().requires_grad_(True)
+    br = b.float().requires_grad_(True)
+    ref = F.cross_entropy(xr @ wr.t() + br, labels.long(), ignore_index=-1)
+    (ref * 1024.0).backward()
+    torch.testing.assert_close(loss, ref.detach(), rtol=2e-3, atol=2e-3)
+
+    def rel(a, r):
+        return float((a.float() - r).norm() / r.norm())
+    assert rel(x.grad, xr.grad) < 2e-2, rel(x.grad, xr.grad)
+    assert rel(wg, wr.grad) < 2e-2, rel(wg, wr.grad)
+    assert rel(bg, br.grad) < 2e-2, rel(bg, br.grad)
+    # the tail of the distribution is not flushed: columns that are nobody's label still get their share
+    unlabelled = torch.ones(V, dtype=torch.bool, device='cuda')
+    unlabelled[labels[labels >= 0].long()] = False
+    assert rel(bg[unlabelled], br.grad[unlabelled]) < 5e-2
+
+
 @pytest.mark.parametrize('dt', DT)
 def test_colsum_gather_scatter(nat, dt):
     M, N = 1000, 776

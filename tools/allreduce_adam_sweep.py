@@ -4,8 +4,9 @@
 
   nccl   : NCCL all-reduce of the flat fp32 gradient + grad-norm + replicated fused Adam (the baseline path;
            what the reference does with DDP + its per-tensor optimizer loop, minus the launch overhead)
-  fused  : in-kernel reduce-scatter over NVLink peer memory + norm exchange + sharded Adam whose epilogue
-           stores the fp16 parameters into every rank (no NCCL call)
+  fused  : in-kernel reduce-scatter + norm exchange + sharded Adam whose epilogue stores the fp16 parameters
+           into every rank (no NCCL call), once with NVLS (multimem.ld_reduce / multimem.st through the switch)
+           and once with plain peer loads / stores
 
 and report the fused path against its roofline = max(bytes over NVLink / link bandwidth, shard HBM bytes /
 measured HBM bandwidth). Launch: python -m torch.distributed.run --nproc-per-node N tools/allreduce_adam_sweep.py
@@ -27,6 +28,7 @@ def main():
     ap.add_argument('--link-gbs', type=float, default=770.0, help='measured NVLink peer bandwidth per direction')
     ap.add_argument('--hbm-gbs', type=float, default=6533.5)
     ap.add_argument('--out', default=None)
+    ap.add_argument('--arms', default='nccl,fused-multimem,fused-p2p')
     a = ap.parse_args()
     rank, world, local = int(os.environ['RANK']), int(os.environ['WORLD_SIZE']), int(os.environ['LOCAL_RANK'])
     torch.cuda.set_device(local)
@@ -40,14 +42,17 @@ def main():
     for mb in [float(x) for x in a.sizes_mb.split(',')]:
         n = int(mb * (1 << 20) / 4)
         res = {'grad_mb': mb, 'n_params': n, 'world': world}
-        for backend in ('nccl', 'fused'):
+        for backend in a.arms.split(','):
+            fused = backend.startswith('fused')
+            if fused:
+                os.environ['HETSEQ_DP_TRANSPORT'] = backend.split('-')[1]
             args = options.make_args('mnist', 'adam', argv=['--lr', '1e-4', '--fp16', '--distributed-world-size', str(world),
-                                                              '--distributed-rank', str(rank), '--dp-backend', backend,
+                                                              '--distributed-rank', str(rank), '--dp-backend', 'fused' if fused else 'nccl',
                                                               '--bucket-cap-mb', '64'])
             p = torch.nn.Parameter(torch.zeros(n, dtype=torch.float16, device=dev))
             buf = FlatParamBuffer([p], world_size=world, rank=rank,
-                                  allocator=fused_dp.symmetric_allocator(args) if backend == 'fused' else None)
-            dp = fused_dp.FusedBackend(args, buf) if backend == 'fused' else data_parallel.AllReduceBackend(args, buf)
+                                  allocator=fused_dp.symmetric_allocator(args) if fused else None)
+            dp = fused_dp.FusedBackend(args, buf) if fused else data_parallel.AllReduceBackend(args, buf)
             opt = _Adam(args, buf, dp=dp)
             ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             eva, evb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -65,6 +70,8 @@ def main():
                 opt.clip_grad_norm(1.0)
                 evb.record()
                 opt.launch_update()
+                if fused:
+                    dp.flush(sync=False)          # the update normally rides next to the next forward pass
                 ev1.record()
                 torch.cuda.synchronize()
                 opt.finish_update(False)
@@ -87,8 +94,11 @@ def main():
         hbm = n / world * (4 * 4 + 3 * 4 + 2) + nbytes / world       # m,v,master,grad read; m,v,master write; param; RS local
         t_hbm = hbm / (a.hbm_gbs * 1e9) * 1e3
         res['roofline_ms'] = round(max(t_link, t_hbm), 4)
-        res['fused_roofline_frac'] = round(res['roofline_ms'] / res['fused_ms'], 3)
-        res['speedup_vs_nccl'] = round(res['nccl_ms'] / res['fused_ms'], 3)
+        for arm in a.arms.split(','):
+            if arm.startswith('fused'):
+                res[arm + '_roofline_frac'] = round(res['roofline_ms'] / res[arm + '_ms'], 3)
+                if 'nccl_ms' in res:
+                    res[arm + '_speedup_vs_nccl'] = round(res['nccl_ms'] / res[arm + '_ms'], 3)
         rows.append(res)
         if rank == 0:
             print(json.dumps(res), flush=True)
