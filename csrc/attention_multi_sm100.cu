@@ -1,5 +1,5 @@
-// hetseq_b200 -- fused masked-softmax attention for sequence lengths of 2..4 tiles of 128 (BERT phase 2:
-// S = 512), head_dim 64, on tcgen05. Same math and the same Philox dropout stream as attention_sm100.cu
+// hetseq_b200 -- fused masked-softmax attention for any sequence length that is a multiple of 16 up to 512
+// (1..4 tiles of 128 rows, the last one possibly partial; BERT phase 2: S = 512), head_dim 64, on tcgen05. Same math and the same Philox dropout stream as attention_sm100.cu
 // (reference: bert_modeling.py:351-377), which keeps the single-tile S = 128 case.
 //
 //   forward    one CTA per (batch, head, query tile). Pass 1 walks the key tiles computing only the row maximum
@@ -15,7 +15,9 @@
 //              Both recompute S, dP = dO V^T, P and dS per (i, j) pair exactly like the single-tile kernel.
 //
 // The [S,S] score matrix never exists in global memory; HBM traffic is the packed QKV projection, O, dO and
-// the gradients, each tile read n = S/128 times.
+// the gradients, each tile read n = ceil(S/128) times. Tiles come through 3-D tensor maps [B][S][cols]: the rows
+// of a partial last tile beyond S are out of bounds and arrive as zeros (never the next sequence's rows); the
+// padded key columns get -inf in the mask, the padded query rows p = 0 in backward and no stores anywhere.
 #include "common.cuh"
 #include "host.h"
 #include "../include/hetseq_b200.h"
@@ -101,7 +103,7 @@ attn_fwd_multi_kernel(const __grid_constant__ CUtensorMap tmQKV, const MultiPara
     tmem_alloc(tmem_slot, 256);
   }
   pdl_sync();   // set-up above overlapped the previous kernel's tail; global memory only from here on
-  for (int i = tid; i < P.S; i += MTHREADS) sMask[i] = P.mask[b * P.S + i] * LOG2E;
+  for (int i = tid; i < n * MT; i += MTHREADS) sMask[i] = i < P.S ? P.mask[b * P.S + i] * LOG2E : -INFINITY;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -119,8 +121,8 @@ attn_fwd_multi_kernel(const __grid_constant__ CUtensorMap tmQKV, const MultiPara
   for (int j = 0; j < n; ++j) {
     if (tid == 0) {
       mbar_expect_tx(&bars[0], (j == 0 ? 2 : 1) * MTILE_BYTES);
-      if (j == 0) tma_load_2d(sQ, &tmQKV, &bars[0], h * MD, qrow0);
-      tma_load_2d(sK, &tmQKV, &bars[0], P.H + h * MD, b * P.S + j * MT);
+      if (j == 0) tma_load_3d(sQ, &tmQKV, &bars[0], h * MD, qi * MT, b);
+      tma_load_3d(sK, &tmQKV, &bars[0], P.H + h * MD, j * MT, b);
       mbar_wait(&bars[0], ph_load);
       tc_fence_after();
       const uint64_t aq = umma_desc_sw128(smem_u32(sQ), 16, 1024);
@@ -162,8 +164,8 @@ attn_fwd_multi_kernel(const __grid_constant__ CUtensorMap tmQKV, const MultiPara
     if (tid == 0) {
       tc_fence_after();
       mbar_expect_tx(&bars[0], 2 * MTILE_BYTES);
-      tma_load_2d(sK, &tmQKV, &bars[0], P.H + h * MD, b * P.S + j * MT);
-      tma_load_2d(sV, &tmQKV, &bars[0], 2 * P.H + h * MD, b * P.S + j * MT);
+      tma_load_3d(sK, &tmQKV, &bars[0], P.H + h * MD, j * MT, b);
+      tma_load_3d(sV, &tmQKV, &bars[0], 2 * P.H + h * MD, j * MT, b);
       mbar_wait(&bars[0], ph_load);
       tc_fence_after();
       const uint64_t aq = umma_desc_sw128(smem_u32(sQ), 16, 1024);
@@ -222,9 +224,10 @@ attn_fwd_multi_kernel(const __grid_constant__ CUtensorMap tmQKV, const MultiPara
   sRed[hf * MT + r] = l;
   __syncthreads();
   l += sRed[(hf ^ 1) * MT + r];
-  if (P.lse && hf == 0)
+  const bool row_ok = qi * MT + r < P.S;          // rows of a partial last tile beyond S own nothing
+  if (P.lse && hf == 0 && row_ok)
     P.lse[static_cast<size_t>(bh) * P.S + qi * MT + r] = (mx + log2f(l)) * 0.6931471805599453f;
-  {
+  if (row_ok) {
     const float inv_l = 1.f / l;
     T* dst = reinterpret_cast<T*>(P.out) + static_cast<size_t>(qrow0 + r) * P.H + h * MD + hf * 32;
     uint32_t rr[32];
@@ -289,7 +292,7 @@ attn_bwd_multi_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_co
     tmem_alloc(tmem_slot, 512);
   }
   pdl_sync();   // set-up above overlapped the previous kernel's tail; global memory only from here on
-  for (int i = tid; i < P.S; i += MTHREADS) sMask[i] = P.mask[b * P.S + i] * LOG2E;
+  for (int i = tid; i < n * MT; i += MTHREADS) sMask[i] = i < P.S ? P.mask[b * P.S + i] * LOG2E : -INFINITY;
   if (tid < 2 * MD) sBias[tid] = 0.f;
   tc_fence_before();
   __syncthreads();
@@ -311,6 +314,11 @@ attn_bwd_multi_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_co
   // per-row quantities of a query tile: log-sum-exp and D = rowsum(dO * O)
   float lse2 = 0.f, Dq = 0.f;
   auto row_stats = [&](int qt) {
+    if (qt * MT + r >= P.S) {      // padded query row: p = exp2(.. - inf) = 0, so it adds nothing to dK / dV
+      Dq = 0.f;
+      lse2 = INFINITY;
+      return;
+    }
     const size_t grow = static_cast<size_t>(b) * P.S + qt * MT + r;
     const T* o = reinterpret_cast<const T*>(P.o) + grow * P.H + h * MD;
     const T* d = reinterpret_cast<const T*>(P.dout) + grow * P.H + h * MD;
@@ -332,16 +340,16 @@ attn_bwd_multi_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_co
     const int kt = MODE == 0 ? outer : it;       // key tile of this step
     if (tid == 0) {
       tc_fence_after();
-      const int qrow = b * P.S + qt * MT, krow = b * P.S + kt * MT;
+      const int qrow = qt * MT, krow = kt * MT;      // row inside the sequence; the batch is the third coordinate
       const bool load_q = MODE == 0 || it == 0, load_k = MODE == 1 || it == 0;
       mbar_expect_tx(&bars[0], ((load_q ? 2 : 0) + (load_k ? 2 : 0)) * MTILE_BYTES);
       if (load_q) {
-        tma_load_2d(sQ, &tmQKV, &bars[0], h * MD, qrow);
-        tma_load_2d(sDO, &tmDO, &bars[0], h * MD, qrow);
+        tma_load_3d(sQ, &tmQKV, &bars[0], h * MD, qrow, b);
+        tma_load_3d(sDO, &tmDO, &bars[0], h * MD, qrow, b);
       }
       if (load_k) {
-        tma_load_2d(sK, &tmQKV, &bars[0], P.H + h * MD, krow);
-        tma_load_2d(sV, &tmQKV, &bars[0], 2 * P.H + h * MD, krow);
+        tma_load_3d(sK, &tmQKV, &bars[0], P.H + h * MD, krow, b);
+        tma_load_3d(sV, &tmQKV, &bars[0], 2 * P.H + h * MD, krow, b);
       }
       mbar_wait(&bars[0], ph_load);
       tc_fence_after();
@@ -473,14 +481,16 @@ attn_bwd_multi_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_co
       uint32_t rr[32];
       tmem_ld_32x32(t_row + 256 + a * 64 + hf * 32, rr);
       tmem_ld_wait();
+      if (outer * MT + r < P.S) {
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        uint4 u;
-        u.x = Cvt<T>::pack2(__uint_as_float(rr[i * 8 + 0]), __uint_as_float(rr[i * 8 + 1]));
-        u.y = Cvt<T>::pack2(__uint_as_float(rr[i * 8 + 2]), __uint_as_float(rr[i * 8 + 3]));
-        u.z = Cvt<T>::pack2(__uint_as_float(rr[i * 8 + 4]), __uint_as_float(rr[i * 8 + 5]));
-        u.w = Cvt<T>::pack2(__uint_as_float(rr[i * 8 + 6]), __uint_as_float(rr[i * 8 + 7]));
-        reinterpret_cast<uint4*>(dst)[i] = u;
+        for (int i = 0; i < 4; ++i) {
+          uint4 u;
+          u.x = Cvt<T>::pack2(__uint_as_float(rr[i * 8 + 0]), __uint_as_float(rr[i * 8 + 1]));
+          u.y = Cvt<T>::pack2(__uint_as_float(rr[i * 8 + 2]), __uint_as_float(rr[i * 8 + 3]));
+          u.z = Cvt<T>::pack2(__uint_as_float(rr[i * 8 + 4]), __uint_as_float(rr[i * 8 + 5]));
+          u.w = Cvt<T>::pack2(__uint_as_float(rr[i * 8 + 6]), __uint_as_float(rr[i * 8 + 7]));
+          reinterpret_cast<uint4*>(dst)[i] = u;
+        }
       }
       if (P.dbias != nullptr) {
         float cs[32];
@@ -519,26 +529,35 @@ int prepare_kernel(K kern, int smem, bool* done) {
 
 }  // namespace
 
-int make_tmap_2d_16b(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t ld,
-                     uint32_t box_inner, uint32_t box_outer);
-
 bool attn_multi_supported(int S, int head_dim) {
-  return head_dim == MD && S > MT && S % MT == 0 && S <= MAX_S;
+  return head_dim == MD && S >= 16 && S % 16 == 0 && S <= MAX_S;
+}
+
+// cudaFuncSetAttribute is per device: remember which devices have been prepared for which kernel
+template <typename K>
+static int prepare_on_device(K kern, int smem, bool (&done)[64]) {
+  int dev = 0;
+  HS_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return prepare_kernel(kern, smem, &done[63]) ;
+  return prepare_kernel(kern, smem, &done[dev]);
 }
 
 int attn_multi_fwd(const void* qkv, const float* mask, void* ctx, float* lse, int B, int S, int heads, int H,
                    float dropout_p, const long long* seed, unsigned site, int dtype, cudaStream_t s) {
   CUtensorMap tm;
-  if (make_tmap_2d_16b(&tm, qkv, 3ull * H, static_cast<uint64_t>(B) * S, 3ull * H, 64, MT)) return 1;
-  MultiParams P{mask, ctx, nullptr, nullptr, lse, nullptr, B, heads, H, S, S / MT, 0.125f, dropout_p, seed, site};
-  const int grid = B * heads * (S / MT);
+  if (make_tmap_3d_16b(&tm, qkv, 3ull * H, static_cast<uint64_t>(S), static_cast<uint64_t>(B), 3ull * H,
+                       3ull * H * S, 64, MT)) return 1;
+  const int nt = (S + MT - 1) / MT;
+  const float scale = 1.0f / sqrtf(static_cast<float>(H / heads));      // 1/sqrt(d), bert_modeling.py:361-362
+  MultiParams P{mask, ctx, nullptr, nullptr, lse, nullptr, B, heads, H, S, nt, scale, dropout_p, seed, site};
+  const int grid = B * heads * nt;
   if (dtype == HS_F16) {
-    static bool done = false;
-    if (prepare_kernel(attn_fwd_multi_kernel<__half>, MULTI_FWD_SMEM, &done)) return 1;
+    static bool done[64] = {false};
+    if (prepare_on_device(attn_fwd_multi_kernel<__half>, MULTI_FWD_SMEM, done)) return 1;
     (void)launch_k(attn_fwd_multi_kernel<__half>, dim3(grid), dim3(MTHREADS), MULTI_FWD_SMEM, s, tm, P);
   } else if (dtype == HS_BF16) {
-    static bool done = false;
-    if (prepare_kernel(attn_fwd_multi_kernel<__nv_bfloat16>, MULTI_FWD_SMEM, &done)) return 1;
+    static bool done[64] = {false};
+    if (prepare_on_device(attn_fwd_multi_kernel<__nv_bfloat16>, MULTI_FWD_SMEM, done)) return 1;
     (void)launch_k(attn_fwd_multi_kernel<__nv_bfloat16>, dim3(grid), dim3(MTHREADS), MULTI_FWD_SMEM, s, tm, P);
   } else { set_last_error("hs_attention_fwd: dtype must be f16 or bf16"); return 1; }
   return post_launch("attn_fwd_multi_kernel");
@@ -548,15 +567,19 @@ int attn_multi_bwd(const void* qkv, const float* mask, const void* ctx, const vo
                    void* dqkv, float* dbias, int B, int S, int heads, int H, float dropout_p, const long long* seed,
                    unsigned site, int dtype, cudaStream_t s) {
   CUtensorMap tmQ, tmD;
-  if (make_tmap_2d_16b(&tmQ, qkv, 3ull * H, static_cast<uint64_t>(B) * S, 3ull * H, 64, MT)) return 1;
-  if (make_tmap_2d_16b(&tmD, dctx, static_cast<uint64_t>(H), static_cast<uint64_t>(B) * S, static_cast<uint64_t>(H), 64, MT)) return 1;
-  MultiParams P{mask, dqkv, ctx, dctx, const_cast<float*>(lse), dbias, B, heads, H, S, S / MT, 0.125f, dropout_p, seed, site};
-  const int grid = B * heads * (S / MT);
+  if (make_tmap_3d_16b(&tmQ, qkv, 3ull * H, static_cast<uint64_t>(S), static_cast<uint64_t>(B), 3ull * H,
+                       3ull * H * S, 64, MT)) return 1;
+  if (make_tmap_3d_16b(&tmD, dctx, static_cast<uint64_t>(H), static_cast<uint64_t>(S), static_cast<uint64_t>(B),
+                       static_cast<uint64_t>(H), static_cast<uint64_t>(H) * S, 64, MT)) return 1;
+  const int nt = (S + MT - 1) / MT;
+  const float scale = 1.0f / sqrtf(static_cast<float>(H / heads));
+  MultiParams P{mask, dqkv, ctx, dctx, const_cast<float*>(lse), dbias, B, heads, H, S, nt, scale, dropout_p, seed, site};
+  const int grid = B * heads * nt;
 #define HS_MULTI_BWD(T)                                                                                  \
   do {                                                                                                   \
-    static bool d0 = false, d1 = false;                                                                  \
-    if (prepare_kernel(attn_bwd_multi_kernel<T, 0>, MULTI_BWD_SMEM, &d0)) return 1;                      \
-    if (prepare_kernel(attn_bwd_multi_kernel<T, 1>, MULTI_BWD_SMEM, &d1)) return 1;                      \
+    static bool d0[64] = {false}, d1[64] = {false};                                                      \
+    if (prepare_on_device(attn_bwd_multi_kernel<T, 0>, MULTI_BWD_SMEM, d0)) return 1;                    \
+    if (prepare_on_device(attn_bwd_multi_kernel<T, 1>, MULTI_BWD_SMEM, d1)) return 1;                    \
     (void)launch_k(attn_bwd_multi_kernel<T, 0>, dim3(grid), dim3(MTHREADS), MULTI_BWD_SMEM, s, tmQ, tmD, P);                     \
     if (post_launch("attn_bwd_multi_kernel<dKdV>")) return 1;                                            \
     (void)launch_k(attn_bwd_multi_kernel<T, 1>, dim3(grid), dim3(MTHREADS), MULTI_BWD_SMEM, s, tmQ, tmD, P);                     \

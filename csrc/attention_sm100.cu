@@ -15,8 +15,9 @@
 //             dV = P^T dO and dK = dS^T Q) -> dQ,dK,dV written into the packed [M,3H] gradient.
 //
 // The score matrix never leaves the SM. This file holds the single-tile kernels (sequence length 128, BERT
-// phase 1); sequence lengths of 2..4 tiles are handled by attention_multi_sm100.cu, to which the host entry
-// points below dispatch. Anything else is reported as unsupported by hs_attention_supported().
+// phase 1); every other sequence length that is a multiple of 16 up to 512 is handled by
+// attention_multi_sm100.cu (1..4 tiles, partial last tile), to which the host entry points below dispatch.
+// Anything else (head_dim != 64, S > 512, S % 16 != 0) is reported as unsupported by hs_attention_supported().
 #include "common.cuh"
 #include "host.h"
 #include "../include/hetseq_b200.h"
@@ -441,6 +442,20 @@ static bool multi_enabled() {
   return on;
 }
 
+// shared-memory opt-in and carve-out are function attributes PER DEVICE: do it once for every device used
+template <typename K>
+static int prepare_attn(K kern, int smem, bool (&done)[64]) {
+  int dev = 0;
+  HS_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) dev = 63;
+  if (!done[dev]) {
+    HS_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    HS_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    done[dev] = true;
+  }
+  return 0;
+}
+
 static int attn_check(const char* who, int B, int S, int heads, int H) {
   if (S != AT_S || heads <= 0 || H != heads * AT_D || B <= 0) {
     set_last_error("%s: unsupported shape B=%d S=%d heads=%d H=%d (needs S=%d, head_dim=%d)", who, B, S, heads, H, AT_S, AT_D);
@@ -467,16 +482,17 @@ extern "C" int hs_attention_fwd(const void* qkv, const float* mask, void* ctx, f
   if (attn_check("hs_attention_fwd", B, S, heads, H)) return 1;
   CUtensorMap tm;
   if (make_tmap_2d_16b(&tm, qkv, 3ull * H, static_cast<uint64_t>(B) * S, 3ull * H, 64, AT_S)) return 1;
-  AttnParams P{mask, ctx, nullptr, nullptr, lse, nullptr, B, heads, H, 0.125f, dropout_p, seed, site};
+  const float scale = 1.0f / sqrtf(static_cast<float>(H / heads));      // 1/sqrt(d), bert_modeling.py:361-362
+  AttnParams P{mask, ctx, nullptr, nullptr, lse, nullptr, B, heads, H, scale, dropout_p, seed, site};
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const int grid = B * heads;
   if (dtype == HS_F16) {
-    static bool done = false;
-    if (!done) { HS_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATTN_FWD_SMEM)); HS_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<__half>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared)); done = true; }
+    static bool done[64] = {false};
+    if (prepare_attn(attn_fwd_kernel<__half>, ATTN_FWD_SMEM, done)) return 1;
     (void)launch_k(attn_fwd_kernel<__half>, dim3(grid), dim3(AT_THREADS), ATTN_FWD_SMEM, s, tm, P);
   } else if (dtype == HS_BF16) {
-    static bool done = false;
-    if (!done) { HS_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATTN_FWD_SMEM)); HS_CUDA_OK(cudaFuncSetAttribute(attn_fwd_kernel<__nv_bfloat16>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared)); done = true; }
+    static bool done[64] = {false};
+    if (prepare_attn(attn_fwd_kernel<__nv_bfloat16>, ATTN_FWD_SMEM, done)) return 1;
     (void)launch_k(attn_fwd_kernel<__nv_bfloat16>, dim3(grid), dim3(AT_THREADS), ATTN_FWD_SMEM, s, tm, P);
   } else { set_last_error("hs_attention_fwd: dtype must be f16 or bf16"); return 1; }
   return post_launch("attn_fwd_kernel");
@@ -499,16 +515,17 @@ extern "C" int hs_attention_bwd(const void* qkv, const float* mask, const void* 
   CUtensorMap tmQ, tmD;
   if (make_tmap_2d_16b(&tmQ, qkv, 3ull * H, static_cast<uint64_t>(B) * S, 3ull * H, 64, AT_S)) return 1;
   if (make_tmap_2d_16b(&tmD, dctx, static_cast<uint64_t>(H), static_cast<uint64_t>(B) * S, static_cast<uint64_t>(H), 64, AT_S)) return 1;
-  AttnParams P{mask, dqkv, ctx, dctx, const_cast<float*>(lse), dbias, B, heads, H, 0.125f, dropout_p, seed, site};
+  const float scale = 1.0f / sqrtf(static_cast<float>(H / heads));
+  AttnParams P{mask, dqkv, ctx, dctx, const_cast<float*>(lse), dbias, B, heads, H, scale, dropout_p, seed, site};
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const int grid = B * heads;
   if (dtype == HS_F16) {
-    static bool done = false;
-    if (!done) { HS_CUDA_OK(cudaFuncSetAttribute(attn_bwd_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATTN_BWD_SMEM)); HS_CUDA_OK(cudaFuncSetAttribute(attn_bwd_kernel<__half>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared)); done = true; }
+    static bool done[64] = {false};
+    if (prepare_attn(attn_bwd_kernel<__half>, ATTN_BWD_SMEM, done)) return 1;
     (void)launch_k(attn_bwd_kernel<__half>, dim3(grid), dim3(AT_THREADS), ATTN_BWD_SMEM, s, tmQ, tmD, P);
   } else if (dtype == HS_BF16) {
-    static bool done = false;
-    if (!done) { HS_CUDA_OK(cudaFuncSetAttribute(attn_bwd_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATTN_BWD_SMEM)); HS_CUDA_OK(cudaFuncSetAttribute(attn_bwd_kernel<__nv_bfloat16>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared)); done = true; }
+    static bool done[64] = {false};
+    if (prepare_attn(attn_bwd_kernel<__nv_bfloat16>, ATTN_BWD_SMEM, done)) return 1;
     (void)launch_k(attn_bwd_kernel<__nv_bfloat16>, dim3(grid), dim3(AT_THREADS), ATTN_BWD_SMEM, s, tmQ, tmD, P);
   } else { set_last_error("hs_attention_bwd: dtype must be f16 or bf16"); return 1; }
   return post_launch("attn_bwd_kernel");

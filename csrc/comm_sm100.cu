@@ -539,6 +539,12 @@ static int fill_table(PeerTable* t, void* const* ptrs, int W) {
 }
 
 static long long gather_blocks(long long nblocks, int ngather) { return (nblocks + ngather - 1) / ngather; }
+// number of NON-EMPTY gather buckets: with blocks_per_gather rounded up the last requested buckets may own
+// no block at all, and a bucket nobody works on is never published
+static int gather_count(long long nblocks, int ngather) {
+  const long long bpg = gather_blocks(nblocks, ngather);
+  return static_cast<int>((nblocks + bpg - 1) / bpg);
+}
 
 }  // namespace hs
 
@@ -636,7 +642,8 @@ extern "C" int hs_dp_update_allgather(int opt, const float* grad, float* master,
     return 1;
   }
   a.grad = grad; a.master = master; a.s1 = state1; a.s2 = state2; a.params_mc = params_mc;
-  a.W = W; a.chunk = chunk; a.ngather = ngather; a.nblocks = nblocks; a.blocks_per_gather = gather_blocks(nblocks, ngather);
+  a.W = W; a.chunk = chunk; a.ngather = gather_count(nblocks, ngather); a.nblocks = nblocks;
+  a.blocks_per_gather = gather_blocks(nblocks, ngather);
   a.h = DpHyper{lr, a_coef, b_coef, eps, weight_decay, step_factor};
   a.scalars = scalars; a.hyper_dev = hyper_dev; a.counters = counters; a.pending = pending;
   int grid = grid_blocks > 0 ? grid_blocks : num_sms() * 8;
@@ -655,9 +662,14 @@ extern "C" int hs_dp_update_allgather(int opt, const float* grad, float* master,
 
 extern "C" int hs_dp_gather_bucket_of(long long nblocks, int ngather, long long block) {
   const long long bpg = gather_blocks(nblocks, ngather);
+  const int n = gather_count(nblocks, ngather);
   long long j = block / bpg;
-  if (j >= ngather) j = ngather - 1;
+  if (j >= n) j = n - 1;
   return static_cast<int>(j);
+}
+extern "C" int hs_dp_gather_count(long long nblocks, int ngather) {
+  if (nblocks <= 0 || ngather <= 0) return 0;
+  return gather_count(nblocks, ngather);
 }
 
 extern "C" int hs_dp_wait_params(void* const* sig_ptrs, int rank, int W, int j_lo, int j_hi, unsigned epoch,
@@ -692,6 +704,7 @@ extern "C" int hs_dp_emulate_step(int W, int blocks_per_rank, void* const* grad_
   e.total_chunks = total_chunks; e.chunks_per_bucket = chunks_per_bucket;
   e.nbuckets = static_cast<int>((total_chunks + chunks_per_bucket - 1) / chunks_per_bucket);
   e.nblocks = total_chunks / W; e.blocks_per_gather = gather_blocks(e.nblocks, ngather);
+  e.ngather = gather_count(e.nblocks, ngather);
   e.norm.sigs = e.sigs; e.norm.W = W; e.norm.mult_host = mult_host; e.norm.max_norm = max_norm; e.norm.mult_dev = nullptr;
   e.h = DpHyper{lr, a_coef, b_coef, eps, weight_decay, step_factor};
   e.hyper_dev = nullptr; e.barrier_words = barrier_words; e.epoch = epoch;

@@ -5,7 +5,12 @@
 // launches (atomic scatter-add into [V,H]) backward.
 //   hs_embed_gather_sum    z[m,:] = W[ids[m],:] + P[m % S,:] + T[seg[m],:]        (LayerNorm + dropout
 //                          follow through hs_ln_fwd(post_dropout=1), the gradient through hs_ln_bwd)
-//   hs_embed_scatter_word  dW[ids[m],:] += de[m,:]   fp32 vector atomics straight into the flat main-grad
+//   hs_embed_scatter_word_sorted  dW[id,:] += sum of de[m,:] over the positions m holding token id, as a segmented
+//                          reduction over the positions SORTED by token id: one thread per (run of equal ids,
+//                          8 columns) adds the rows of its run in ascending position order and is the only writer
+//                          of its slice of dW -- deterministic, no atomics. The order and the run
+//                          boundaries come from the host (computed in the batch-prefetch thread) or from a device sort.
+//   hs_embed_scatter_word  the same sum with fp32 vector atomics (order of additions varies from run to run)
 //   hs_sum_over_batch      dP[s,:] (+)= sum_b de[b*S+s,:]            deterministic, no atomics
 //   hs_colsum_rows_where   dT[t,:] (+)= sum_{m: seg[m]==t} de[m,:]   deterministic two-stage column sum
 // Token ids arrive as int32 (the trainer narrows them before the host->device copy) or int64.
@@ -61,6 +66,48 @@ embed_scatter_word_kernel(const T* __restrict__ de, const IdT* __restrict__ ids,
   float4* dst = reinterpret_cast<float4*>(dW + static_cast<size_t>(id) * H + c * 8);
   atomicAdd(dst, make_float4(f[0], f[1], f[2], f[3]));
   atomicAdd(dst + 1, make_float4(f[4], f[5], f[6], f[7]));
+}
+
+// order[i]: position (row of de) that is i-th when positions are sorted by token id (stable: ties in ascending
+// position). run_end[i]: for the FIRST sorted slot of a run of equal ids, one past its last slot; 0 elsewhere.
+template <typename T, typename IdT>
+__global__ void __launch_bounds__(256)
+embed_scatter_sorted_kernel(const T* __restrict__ de, const IdT* __restrict__ ids, const int* __restrict__ order,
+                            const int* __restrict__ run_end, float* __restrict__ dW, int M, int H, int vocab) {
+  const int vpr = H >> 3;
+  const long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const int i = static_cast<int>(t / vpr), c = static_cast<int>(t % vpr);
+  if (i >= M) return;
+  const int e = min(run_end[i], M);
+  if (e <= i) return;                     // not the first slot of a run
+  const int p0 = order[i];
+  if (p0 < 0 || p0 >= M) return;
+  const long long id = static_cast<long long>(ids[p0]);
+  if (id < 0 || id >= vocab) return;
+  float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  constexpr int U = 8;                    // rows in flight per thread; a warp reads 512 contiguous bytes of each row
+  for (int j = i; j < e; j += U) {
+    int p[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) p[u] = j + u < e ? order[j + u] : -1;
+    uint4 v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      v[u] = (p[u] >= 0 && p[u] < M) ? reinterpret_cast<const uint4*>(de + static_cast<size_t>(p[u]) * H)[c] : make_uint4(0, 0, 0, 0);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {          // ascending slot order: the sum is the same on every run
+      float f[8];
+      unpack8e<T>(v[u], f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[k] += f[k];
+    }
+  }
+  float4* dst = reinterpret_cast<float4*>(dW + static_cast<size_t>(id) * H + c * 8);
+  float4 a = dst[0], b = dst[1];           // the decoder's weight gradient is already in there (tied matrix)
+  a.x += acc[0]; a.y += acc[1]; a.z += acc[2]; a.w += acc[3];
+  b.x += acc[4]; b.y += acc[5]; b.z += acc[6]; b.w += acc[7];
+  dst[0] = a;
+  dst[1] = b;
 }
 
 template <typename T>
@@ -148,6 +195,25 @@ extern "C" int hs_embed_scatter_word(const void* de, const void* ids, int ids_i6
   else { set_last_error("hs_embed_scatter_word: dtype must be f16 or bf16"); return 1; }
 #undef HS_ES
   return post_launch("embed_scatter_word_kernel");
+}
+
+extern "C" int hs_embed_scatter_word_sorted(const void* de, const void* ids, int ids_i64, const int* order,
+                                            const int* run_end, float* dW, int M, int H, int vocab, int dtype,
+                                            hs_stream_t stream) {
+  if (M <= 0 || H % 8 != 0 || order == nullptr || run_end == nullptr) { set_last_error("hs_embed_scatter_word_sorted: bad arguments"); return 1; }
+  const long long total = static_cast<long long>(M) * (H / 8);
+  const int grid = static_cast<int>((total + 255) / 256);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+#define HS_ESS(T)                                                                                                 \
+  do {                                                                                                            \
+    if (ids_i64) embed_scatter_sorted_kernel<T, long long><<<grid, 256, 0, s>>>((const T*)de, (const long long*)ids, order, run_end, dW, M, H, vocab); \
+    else embed_scatter_sorted_kernel<T, int><<<grid, 256, 0, s>>>((const T*)de, (const int*)ids, order, run_end, dW, M, H, vocab); \
+  } while (0)
+  if (dtype == HS_F16) HS_ESS(__half);
+  else if (dtype == HS_BF16) HS_ESS(__nv_bfloat16);
+  else { set_last_error("hs_embed_scatter_word_sorted: dtype must be f16 or bf16"); return 1; }
+#undef HS_ESS
+  return post_launch("embed_scatter_sorted_kernel");
 }
 
 extern "C" int hs_sum_over_batch(const void* x, int B, long long inner, float* out, int accumulate, int dtype,

@@ -591,6 +591,37 @@ static int make_tmap_2d(CUtensorMap* out, const void* base, uint64_t inner, uint
   return 0;
 }
 
+// 3-D tiled map (128-byte swizzle) over a 16-bit tensor [outer][mid][inner] (inner contiguous): a box of
+// box_inner x box_mid x 1 elements lands in shared memory exactly like the 2-D box of make_tmap_2d_16b, but rows
+// beyond `mid` are out of bounds -- zero-filled -- instead of running into the next `outer` slice. The attention
+// kernels use it to read a sequence's last, partial 128-row tile.
+int make_tmap_3d_16b(CUtensorMap* out, const void* base, uint64_t inner, uint64_t mid, uint64_t outer,
+                     uint64_t ld_mid, uint64_t ld_outer, uint32_t box_inner, uint32_t box_mid) {
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) {
+    (void)cudaFree(nullptr);
+    ctx_bound = true;
+  }
+  PFN_encodeTiled enc = get_encode_fn();
+  if (enc == nullptr) {
+    set_last_error("cuTensorMapEncodeTiled is not available from the CUDA driver");
+    return 1;
+  }
+  cuuint64_t dims[3] = {inner, mid, outer};
+  cuuint64_t strides[2] = {ld_mid * 2ull, ld_outer * 2ull};
+  cuuint32_t box[3] = {box_inner, box_mid, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_UINT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_last_error("cuTensorMapEncodeTiled (3-D) failed (%d): base=%p dims=%llu x %llu x %llu", (int)r, base,
+                   (unsigned long long)inner, (unsigned long long)mid, (unsigned long long)outer);
+    return 1;
+  }
+  return 0;
+}
+
 template <int BN, typename InT, typename OutT, int CG>
 static int launch_gemm(const hs_gemm_args& a, cudaStream_t stream) {
   using Cfg = GemmCfg<BN, CG>;

@@ -19,6 +19,10 @@ int colsum_slabs(int M);
 int make_tmap_2d_16b(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t ld,
                      uint32_t box_inner, uint32_t box_outer);
 
+// 3-D variant: [outer][mid][inner], box = box_inner x box_mid x 1; rows >= mid are zero-filled (out of bounds).
+int make_tmap_3d_16b(CUtensorMap* out, const void* base, uint64_t inner, uint64_t mid, uint64_t outer,
+                     uint64_t ld_mid, uint64_t ld_outer, uint32_t box_inner, uint32_t box_mid);
+
 // HETSEQ_PDL=0 switches programmatic dependent launch off (every launch then serialises like <<<>>>).
 bool pdl_enabled();
 

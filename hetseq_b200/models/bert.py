@@ -545,16 +545,21 @@ class BertForPreTraining(BertPreTrainedModel):
         self.native = None  # set by ops.bert_native.attach()
 
     def forward(self, input_ids, token_type_ids=None, attention_mask=None, masked_lm_labels=None,
-                next_sentence_label=None, mlm_rows=None, mlm_row_labels=None, checkpoint_activations=None):
+                next_sentence_label=None, mlm_rows=None, mlm_row_labels=None, emb_order=None, emb_run_end=None,
+                checkpoint_activations=None):
         """``mlm_rows`` / ``mlm_row_labels`` (optional, fixed capacity, padded with -1): flat indices of the
         labelled positions and their labels, precomputed on the host by the task. They remove the
         data-dependent ``nonzero`` (a device->host sync) from the step and give the MLM head a static shape,
-        which is what lets the whole step be captured in a CUDA graph."""
+        which is what lets the whole step be captured in a CUDA graph. ``emb_order`` / ``emb_run_end`` (optional):
+        positions sorted by token id and the run boundaries, for the deterministic scatter of the word-embedding
+        gradient (native path; ignored by the PyTorch path)."""
         ckpt = self.checkpoint_activations if checkpoint_activations is None else checkpoint_activations
         if self.native is not None and masked_lm_labels is not None and next_sentence_label is not None:
             return self.native.pretraining_loss(self, input_ids, token_type_ids, attention_mask,
                                                 masked_lm_labels, next_sentence_label, ckpt,
-                                                mlm_rows=mlm_rows, mlm_row_labels=mlm_row_labels)
+                                                mlm_rows=mlm_rows, mlm_row_labels=mlm_row_labels,
+                                                emb_plan=None if emb_order is None or emb_run_end is None
+                                                else (emb_order, emb_run_end))
         sequence_output, pooled_output = self.bert(input_ids, token_type_ids, attention_mask,
                                                    output_all_encoded_layers=False,
                                                    checkpoint_activations=ckpt)

@@ -327,21 +327,30 @@ class EncoderLayerFn(torch.autograd.Function):
 # ------------------------------------------------------------------------------------------------
 class EmbeddingSumFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, W, P, T, ids, seg, pW, pP, pT, B, S):
+    def forward(ctx, W, P, T, ids, seg, pW, pP, pT, B, S, plan=None):
         z = native.embed_gather_sum(W, P, T, ids, seg, B * S, S)
-        ctx.save_for_backward(ids, seg)
+        if plan is None and os.environ.get('HETSEQ_EMBED_ATOMIC', '0') != '1':
+            plan = native.embedding_scatter_plan(ids)     # device sort; the task normally supplies a host-made plan
+        if plan is None:
+            ctx.save_for_backward(ids, seg)
+        else:
+            ctx.save_for_backward(ids, seg, plan[0].contiguous(), plan[1].contiguous())
         ctx.meta = (pW, pP, pT, B, S)
         return z
 
     @staticmethod
     def backward(ctx, de):
-        ids, seg = ctx.saved_tensors
+        ids, seg = ctx.saved_tensors[:2]
         pW, pP, pT, B, S = ctx.meta
         de = de.contiguous()
         H = de.shape[1]
         bufW = pW._hs_flat[0]
-        dW = bufW.ensure_initialized(pW)          # atomics can only accumulate
-        native.embed_scatter_word(de, ids, dW)
+        dW = bufW.ensure_initialized(pW)          # the scatter adds to what the decoder's wgrad left (tied matrix)
+        if len(ctx.saved_tensors) == 4:
+            # segmented reduction over positions sorted by token id: one writer per (token, column), fixed order
+            native.embed_scatter_word_sorted(de, ids, ctx.saved_tensors[2], ctx.saved_tensors[3], dW)
+        else:
+            native.embed_scatter_word(de, ids, dW)    # fp32 atomics (HETSEQ_EMBED_ATOMIC=1)
         _notify([pW])
         pg, pacc = _wgrad_target([pP])
         pg = pg.view(pP.shape)
@@ -357,7 +366,7 @@ class EmbeddingSumFn(torch.autograd.Function):
         for t in range(pT.shape[0]):
             native.colsum_rows_where(de, seg, t, tg[t], tacc)
         _notify([pT])
-        return None, None, None, None, None, None, None, None, None, None
+        return None, None, None, None, None, None, None, None, None, None, None
 
 
 # ------------------------------------------------------------------------------------------------
@@ -535,9 +544,12 @@ class NativeBert(object):
         ids = input_ids.reshape(-1).contiguous()
         seg = token_type_ids.reshape(-1).to(ids.dtype).contiguous()
         self.buffer.gate(self.gate_params['emb'])
+        plan, self._emb_plan = getattr(self, '_emb_plan', None), None
+        if plan is not None and (plan[0].numel() != ids.numel() or plan[0].device != ids.device):
+            plan = None
         z = EmbeddingSumFn.apply(emb.word_embeddings.weight, emb.position_embeddings.weight,
                                  emb.token_type_embeddings.weight, ids, seg, emb.word_embeddings.weight,
-                                 emb.position_embeddings.weight, emb.token_type_embeddings.weight, B, S)
+                                 emb.position_embeddings.weight, emb.token_type_embeddings.weight, B, S, plan)
         p_h = self.p_hidden if bert.training else 0.0
         x = drop_add_ln(z, None, emb.LayerNorm, p_h, self.site_emb, post=True).view(B, S, self.H)
         add_mask = ((1.0 - attention_mask.to(torch.float32)) * -10000.0).contiguous()
@@ -556,7 +568,9 @@ class NativeBert(object):
 
     # -- pre-training heads ---------------------------------------------------------------------------
     def pretraining_loss(self, model, input_ids, token_type_ids, attention_mask, masked_lm_labels,
-                         next_sentence_label, checkpoint_activations, mlm_rows=None, mlm_row_labels=None):
+                         next_sentence_label, checkpoint_activations, mlm_rows=None, mlm_row_labels=None,
+                         emb_plan=None):
+        self._emb_plan = emb_plan      # (order, run_end) of the deterministic word-embedding scatter, host-made
         seq, pooled = model.bert(input_ids, token_type_ids, attention_mask, output_all_encoded_layers=False,
                                  checkpoint_activations=checkpoint_activations)
         B, S = input_ids.shape

@@ -136,6 +136,30 @@ def embed_scatter_word(de, ids, dW):
                                       dW.shape[0], lib.dtype_code(de.dtype), lib.stream_ptr()), 'hs_embed_scatter_word')
 
 
+def embed_scatter_word_sorted(de, ids, order, run_end, dW):
+    """dW[id] += sum of de rows holding token id, deterministic (segmented reduction over sorted positions)."""
+    L = lib.load()
+    M, H = de.shape
+    lib.check(L.hs_embed_scatter_word_sorted(de.data_ptr(), ids.data_ptr(), int(ids.dtype == torch.int64),
+                                             order.data_ptr(), run_end.data_ptr(), dW.data_ptr(), M, H, dW.shape[0],
+                                             lib.dtype_code(de.dtype), lib.stream_ptr()), 'hs_embed_scatter_word_sorted')
+
+
+def embedding_scatter_plan(ids_flat: torch.Tensor):
+    """(order, run_end) int32 for ``embed_scatter_word_sorted`` from the token ids, with static-shape tensor ops
+    only (usable on the device inside a captured graph, or on the host in the batch-prefetch thread)."""
+    M = ids_flat.numel()
+    sorted_ids, order = torch.sort(ids_flat.reshape(-1), stable=True)
+    idx = torch.arange(M, device=ids_flat.device)
+    start = torch.ones(M, dtype=torch.bool, device=ids_flat.device)
+    start[1:] = sorted_ids[1:] != sorted_ids[:-1]
+    nxt = torch.where(start, idx, torch.full_like(idx, M))                # index of a run start, M elsewhere
+    shifted = torch.cat([nxt[1:], torch.full((1,), M, dtype=idx.dtype, device=idx.device)])
+    next_start = torch.flip(torch.cummin(torch.flip(shifted, [0]), 0).values, [0])   # first run start after slot i
+    run_end = torch.where(start, next_start, torch.zeros_like(next_start))
+    return order.to(torch.int32), run_end.to(torch.int32)
+
+
 def sum_over_batch(x, B, inner, out, accumulate):
     L = lib.load()
     lib.check(L.hs_sum_over_batch(x.data_ptr(), B, inner, out.data_ptr(), int(accumulate), lib.dtype_code(x.dtype),

@@ -16,6 +16,7 @@ SIGNATURES = {
     'hs_scatter_add_rows': [vp, vp, ci, vp, ci, ci, ci, vp],
     'hs_embed_gather_sum': [vp, vp, vp, vp, vp, ci, vp, ci, ci, ci, ci, ci, ci, vp],
     'hs_embed_scatter_word': [vp, vp, ci, vp, ci, ci, ci, ci, vp],
+    'hs_embed_scatter_word_sorted': [vp, vp, ci, vp, vp, vp, ci, ci, ci, ci, vp],
     'hs_sum_over_batch': [vp, ci, cl, vp, ci, ci, vp],
     'hs_colsum_rows_where': [vp, vp, ci, cl, ci, ci, vp, ci, vp, ci, vp],
     'hs_attention_fwd': [vp, vp, vp, vp, ci, ci, ci, ci, cf, vp, cu, ci, vp],
@@ -30,6 +31,7 @@ SIGNATURES = {
     'hs_dp_update_allgather': [ci, vp, vp, vp, vp, vp, vp, vp, ci, ci, cl, ci, ci, cf, cf, cf, cf, cf, cf, vp, vp, cu,
                                vp, ci, vp, vp, ci, ci, vp],
     'hs_dp_gather_bucket_of': [cl, ci, cl],
+    'hs_dp_gather_count': [cl, ci],
     'hs_dp_wait_params': [vp, ci, ci, ci, ci, cu, vp, ci, vp],
     'hs_dp_emulate_step': [ci, ci, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, cl, cl, ci, ci, ci, ci,
                            cf, cf, cf, cf, cf, cf, cf, cf, cu, vp],

@@ -223,8 +223,10 @@ class FusedBackend(AllReduceBackend):
         self.skip = torch.zeros(1, dtype=torch.int32, device=dev)
         self.pending_dev = torch.zeros(1, dtype=torch.int32, device=dev)
         self.ss_local = torch.zeros(1, dtype=torch.float32, device=dev)
-        self.ngather = max(1, min(int(os.environ.get('HETSEQ_DP_GATHER_BUCKETS', '32')),
-                                  int(self.L.hs_dp_max_gather_buckets()), buffer.num_blocks))
+        self.ngather_req = max(1, min(int(os.environ.get('HETSEQ_DP_GATHER_BUCKETS', '32')),
+                                      int(self.L.hs_dp_max_gather_buckets()), buffer.num_blocks))
+        #: gather buckets that actually hold blocks (only these are published and may be waited for)
+        self.ngather = int(self.L.hs_dp_gather_count(buffer.num_blocks, self.ngather_req))
         self.counters = torch.zeros(self.ngather + 1, dtype=torch.int32, device=dev)
         # default priority (the lowest): the reduce / update kernels must never delay the placement of the
         # forward's and backward's CTAs; they run in whatever the GEMMs leave free
@@ -296,7 +298,7 @@ class FusedBackend(AllReduceBackend):
             float(h['weight_decay']), 1.0, self.scalars.data_ptr(),
             (opt.hyper_t if flush else opt.hyper_prev_t).data_ptr(), 0,
             self.epoch_t.data_ptr(), int(epoch_offset), self.counters.data_ptr(), self.pending_dev.data_ptr(),
-            self.ngather, self.update_blocks, self.update_stream.cuda_stream), 'hs_dp_update_allgather')
+            self.ngather_req, self.update_blocks, self.update_stream.cuda_stream), 'hs_dp_update_allgather')
 
     def gate(self, flat_end: int):
         """Forward-side wait: returns (on the current stream) once every rank's slice of the parameters up to
@@ -304,7 +306,7 @@ class FusedBackend(AllReduceBackend):
         if self._gated >= self.ngather:
             return
         block = max(0, (int(flat_end) - 1) // (self.world_size * CHUNK))
-        j = int(self.L.hs_dp_gather_bucket_of(self.buffer.num_blocks, self.ngather, block))
+        j = int(self.L.hs_dp_gather_bucket_of(self.buffer.num_blocks, self.ngather_req, block))
         if j < self._gated:
             return
         lib.check(self.L.hs_dp_wait_params(self.sig_ptrs, self.rank, self.world_size, self._gated, j, 0,

@@ -142,6 +142,22 @@ class LanguageModelingTask(Task):
         row_labels[:rows.size] = lab[rows]
         return torch.from_numpy(idx), torch.from_numpy(row_labels)
 
+    @staticmethod
+    def embedding_plan(input_ids: torch.Tensor):
+        """Host-side plan of the deterministic word-embedding gradient scatter: positions sorted by token id
+        (stable) and, for the first slot of each run of equal ids, one past the run's end (0 elsewhere). Fixed
+        shape [B*S] each; costs a numpy argsort in the prefetch thread instead of a device sort per step."""
+        flat = input_ids.reshape(-1).numpy()
+        order = np.argsort(flat, kind='stable')
+        sorted_ids = flat[order]
+        n = flat.size
+        start = np.ones(n, dtype=bool)
+        start[1:] = sorted_ids[1:] != sorted_ids[:-1]
+        starts = np.nonzero(start)[0]
+        run_end = np.zeros(n, dtype=np.int32)
+        run_end[starts] = np.append(starts[1:], n)
+        return torch.from_numpy(order.astype(np.int32)), torch.from_numpy(run_end)
+
     def prepare_sample(self, sample, device):
         """int64 on disk, int32 on the wire: token ids and labels fit in 32 bits and the native
         kernels consume int32 directly; PyTorch-path modules widen as needed. Appends
@@ -162,6 +178,7 @@ class LanguageModelingTask(Task):
             sample = self.pad_batch(sample, self.static_batch_size)
         if len(sample) == 5 and sample[3].device.type == 'cpu' and not getattr(self.args, 'mlm_all_positions', False):
             sample += list(self.mlm_index(sample[3]))
+            sample += list(self.embedding_plan(sample[0]))
         if narrow:
             sample = [t.to(torch.int32) if t.dtype == torch.int64 else t for t in sample]
         return sample

@@ -172,15 +172,23 @@ HS_API int hs_embed_gather_sum(const void* W, const void* P, const void* Tt, con
                                hs_stream_t stream);
 HS_API int hs_embed_scatter_word(const void* de, const void* ids, int ids_i64, float* dW, int M, int H, int vocab,
                                  int dtype, hs_stream_t stream);
+/* Deterministic form of the same scatter-add (the reference's embedding_dense_backward is an atomic scatter,
+ * bert_modeling.py:313): order[M] lists the positions sorted by token id (stable), run_end[i] is, for the first
+ * sorted slot of each run of equal ids, one past the run's last slot and 0 for every other slot. One thread per
+ * (run, 8 columns) sums its rows in slot order and adds the result to dW: bit-identical from run to run. */
+HS_API int hs_embed_scatter_word_sorted(const void* de, const void* ids, int ids_i64, const int* order,
+                                        const int* run_end, float* dW, int M, int H, int vocab, int dtype,
+                                        hs_stream_t stream);
 HS_API int hs_sum_over_batch(const void* x, int B, long long inner, float* out, int accumulate, int dtype,
                              hs_stream_t stream);
 HS_API int hs_colsum_rows_where(const void* x, const void* sel, int sel_i64, long long want, int M, int N, float* out,
                                 int accumulate, float* scratch, int dtype, hs_stream_t stream);
 
 /* ---- fused attention on tcgen05 (csrc/attention_sm100.cu; bert_modeling.py:351-377, K2-K4/W4) -------- */
-/* 1 when the fused kernels handle this (sequence length, head dim): head dim 64 and S = 128 (single-tile
- * kernels) or S = 256 / 384 / 512 (multi-tile kernels, attention_multi_sm100.cu; HETSEQ_ATTN_MULTI=0 disables
- * them). Callers must check first. */
+/* 1 when the fused kernels handle this (sequence length, head dim): head dim 64 and S a multiple of 16 up to
+ * 512 -- S = 128 by the single-tile kernels, every other length by the multi-tile kernels
+ * (attention_multi_sm100.cu: 1..4 tiles of 128 rows, the last one partial through out-of-bounds zero fill;
+ * HETSEQ_ATTN_MULTI=0 disables them). Callers must check first. */
 HS_API int hs_attention_supported(int S, int head_dim);
 /* ctx[M,H] = merge_heads(dropout(softmax(Q K^T / sqrt(d) + mask)) V) from the packed projection
  * qkv [M, 3H] (q | k | v column blocks, heads of 64 inside each). mask: [B,S] additive fp32.
@@ -243,8 +251,11 @@ HS_API int hs_dp_update_allgather(int opt, const float* grad, float* master, flo
                                   const float* hyper_dev, unsigned epoch, const unsigned* epoch_dev, int epoch_offset,
                                   unsigned int* counters, int* pending, int ngather, int grid_blocks,
                                   hs_stream_t stream);
-/* Gather bucket that owned block `block` (of nblocks per rank) falls into. */
+/* Gather bucket that owned block `block` (of nblocks per rank) falls into, and the number of non-empty gather
+ * buckets (<= ngather: buckets hold ceil(nblocks / ngather) blocks each, so the last requested ones may be
+ * empty; flags exist, and may be waited for, only for buckets [0, hs_dp_gather_count)). */
 HS_API int hs_dp_gather_bucket_of(long long nblocks, int ngather, long long block);
+HS_API int hs_dp_gather_count(long long nblocks, int ngather);
 /* Returns (on the stream) once gather buckets [j_lo, j_hi] of update `epoch + epoch_offset` have arrived from
  * every rank. The forward pass queues one in front of the first kernel that reads a slice. */
 HS_API int hs_dp_wait_params(void* const* sig_ptrs, int rank, int W, int j_lo, int j_hi, unsigned epoch,

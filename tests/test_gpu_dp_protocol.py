@@ -20,6 +20,17 @@ pytestmark = pytest.mark.gpu
 CHUNK = 2048
 
 
+@pytest.fixture(autouse=True)
+def _short_peer_timeout():
+    """A protocol bug shows up as a wait that never ends: make it a trap after seconds, not after the
+    production default of half an hour."""
+    from hetseq_b200.ops import lib
+    L = lib.load()
+    lib.check(L.hs_dp_set_timeout(15.0), 'hs_dp_set_timeout')
+    yield
+    lib.check(L.hs_dp_set_timeout(1800.0), 'hs_dp_set_timeout')
+
+
 def _ptr_array(tensors, ctype=ctypes.c_void_p):
     arr = (ctype * len(tensors))()
     for i, t in enumerate(tensors):
@@ -46,7 +57,8 @@ class VirtualRanks(object):
         self.scalars = [torch.zeros(8, dtype=torch.float32, device=dev) for _ in range(W)]
         self.skip = [torch.zeros(1, dtype=torch.int32, device=dev) for _ in range(W)]
         self.pending = [torch.zeros(1, dtype=torch.int32, device=dev) for _ in range(W)]
-        self.ngather = 4
+        self.ngather_req = 4
+        self.ngather = int(self.L.hs_dp_gather_count(blocks, self.ngather_req))      # non-empty gather buckets
         self.counters = [torch.zeros(self.ngather + 1, dtype=torch.int32, device=dev) for _ in range(W)]
         self.barrier = torch.zeros(W, dtype=torch.int32, device=dev)
 
@@ -84,7 +96,7 @@ class VirtualRanks(object):
             W, blocks_per_rank, _ptr_array(self.grads), _ptr_array(self.params), _ptr_array(self.sigs),
             _ptr_array(self.sumsq), _ptr_array(self.ss), _ptr_array(self.scalars), _ptr_array(self.skip),
             _ptr_array(self.master), _ptr_array(self.s1), _ptr_array(self.s2), _ptr_array(self.counters),
-            _ptr_array(self.pending), self.barrier.data_ptr(), W * self.blocks, chunks_per_bucket, CHUNK, self.ngather,
+            _ptr_array(self.pending), self.barrier.data_ptr(), W * self.blocks, chunks_per_bucket, CHUNK, self.ngather_req,
             0 if self.opt == 'adam' else 1, self.lib.dtype_code(self.dtype), self.hyper['lr'], a, b, self.hyper['eps'],
             self.hyper['weight_decay'], step_factor, mult_host, max_norm, self.epoch, self.lib.stream_ptr())
         self.lib.check(rc, 'hs_dp_emulate_step')
@@ -181,8 +193,6 @@ def test_wait_params_and_flags_are_epoch_numbered():
     words_param = [3 * W + j * W + src for j in range(vr.ngather) for src in range(W)]
     assert all(int(flags[w]) == 2 for w in words_param)
     # a wait for epoch 2 on rank 0 returns immediately (would trap after the timeout otherwise)
-    lib.check(L.hs_dp_set_timeout(5.0), 'hs_dp_set_timeout')
     lib.check(L.hs_dp_wait_params(_ptr_array(vr.sigs), 0, W, 0, vr.ngather - 1, 2, None, 0, lib.stream_ptr()),
               'hs_dp_wait_params')
     torch.cuda.synchronize()
-    lib.check(L.hs_dp_set_timeout(1800.0), 'hs_dp_set_timeout')

@@ -307,6 +307,19 @@ def test_embedding_kernels(nat, dt):
     nat.embed_scatter_word(de, ids, dW)
     refW = torch.zeros(V, H, device='cuda').index_add_(0, ids.long(), de.float())
     torch.testing.assert_close(dW, refW, rtol=1e-4, atol=1e-4)
+    # deterministic form: segmented reduction over the positions sorted by token id, on top of an existing
+    # gradient (the tied decoder matrix); identical bits on every run, with the plan made on either side
+    from hetseq_b200.tasks.bert import LanguageModelingTask
+    ids[: B * S // 3] = 7                      # one long run, like [PAD]
+    refW = torch.ones(V, H, device='cuda').index_add_(0, ids.long(), de.float())
+    outs = []
+    for plan in (nat.embedding_scatter_plan(ids), [t.cuda() for t in LanguageModelingTask.embedding_plan(ids.cpu())],
+                 nat.embedding_scatter_plan(ids)):
+        dW2 = torch.ones(V, H, device='cuda')
+        nat.embed_scatter_word_sorted(de, ids, plan[0], plan[1], dW2)
+        torch.testing.assert_close(dW2, refW, rtol=1e-4, atol=2e-3)
+        outs.append(dW2)
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2]), 'the sorted scatter must be bit-reproducible'
     dP = torch.zeros(S * H, device='cuda')
     nat.sum_over_batch(de, B, S * H, dP, False)
     torch.testing.assert_close(dP.view(S, H), de.float().view(B, S, H).sum(0), rtol=1e-4, atol=1e-4)
@@ -366,9 +379,11 @@ def _attn_ref(qkv, mask, B, S, heads):
 
 
 @pytest.mark.parametrize('dt', DT)
-@pytest.mark.parametrize('S', [128, 256, 512])
+@pytest.mark.parametrize('S', [128, 256, 512, 48, 96, 208, 400])
 def test_attention_fwd_bwd(dt, S):
-    """S = 128: single-tile kernels; S = 256 / 512: multi-tile kernels (two-pass forward, dK/dV and dQ backward)."""
+    """S = 128: single-tile kernels; every other multiple of 16 up to 512: multi-tile kernels (two-pass forward,
+    dK/dV and dQ backward), including sequence lengths whose last 128-row tile is partial (48, 96, 208, 400: rows
+    beyond S arrive as zeros through the 3-D tensor map and never reach memory)."""
     from hetseq_b200.ops import attention_native as an
     B, heads, d = 3, 4, 64
     H = heads * d
@@ -378,6 +393,8 @@ def test_attention_fwd_bwd(dt, S):
     mask = torch.zeros(B, S, device='cuda')
     mask[0, S - 28:] = -10000.0
     mask[2, 17:] = -10000.0
+    # (with a partial last tile a CTA that wrote rows beyond its own sequence would clobber the next one's: the
+    # comparison of every row below catches that)
     out = an.attention(qkv, mask, B, S, heads, 0.0, 1)
     ref_in = qkv.detach().float().requires_grad_(True)
     ref = _attn_ref(ref_in, mask, B, S, heads)
@@ -407,7 +424,7 @@ def test_attention_fwd_bwd(dt, S):
     torch.testing.assert_close(dbias, ref_in.grad.sum(0) + 1.5, rtol=2e-2, atol=0.05 if dt == torch.float16 else 0.3)
 
 
-@pytest.mark.parametrize('S', [128, 384])
+@pytest.mark.parametrize('S', [128, 384, 80])
 def test_attention_dropout_consistency(S):
     """Dropout: same (seed, site) -> identical output; backward uses the very same mask (checked through
     linearity: with V = ones-like structure the gradient of sum(out) w.r.t. v equals column sums of P_drop)."""
