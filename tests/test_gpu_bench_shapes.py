@@ -108,6 +108,7 @@ def test_loss_curve_native_fp16_tracks_torch_fp32(tmp_path):
             ctl.optimizer.refresh_master()
         else:
             init = {k: v.detach().clone() for k, v in ctl.get_model().state_dict().items()}
+            ctl.optimizer.scaler.loss_scale = 1024.0     # start below the overflow point: no skipped updates
         losses = []
         for it in range(100):
             out = ctl.train_step([batches[it % len(batches)]])
@@ -115,7 +116,7 @@ def test_loss_curve_native_fp16_tracks_torch_fp32(tmp_path):
                 losses.append(out['loss'])
         curves[mode] = losses
     a, b = curves['native'], curves['torch']
-    assert len(b) == 100 and len(a) >= 97, (len(a), len(b))        # at most a few loss-scale skips
+    assert len(b) == 100 and len(a) >= 98, (len(a), len(b))        # hardly any loss-scale skip
     tail_a, tail_b = sum(a[-10:]) / 10, sum(b[-10:]) / 10
     assert tail_b < b[0] - 1.0, 'the fp32 oracle itself must have learned something'
     assert abs(tail_a - tail_b) < 0.05 * tail_b, (tail_a, tail_b)
