@@ -227,14 +227,14 @@ attn_fwd_multi_kernel(const __grid_constant__ CUtensorMap tmQKV, const MultiPara
   const bool row_ok = qi * MT + r < P.S;          // rows of a partial last tile beyond S own nothing
   if (P.lse && hf == 0 && row_ok)
     P.lse[static_cast<size_t>(bh) * P.S + qi * MT + r] = (mx + log2f(l)) * 0.6931471805599453f;
-  if (row_ok) {
+  {
     const float inv_l = 1.f / l;
     T* dst = reinterpret_cast<T*>(P.out) + static_cast<size_t>(qrow0 + r) * P.H + h * MD + hf * 32;
     uint32_t rr[32];
-    tmem_ld_32x32(t_row + 128 + hf * 32, rr);
+    tmem_ld_32x32(t_row + 128 + hf * 32, rr);      // warp-collective (.sync.aligned): never under a per-row condition
     tmem_ld_wait();
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < 4 && row_ok; ++i) {
       uint4 u;
       u.x = Cvt<T>::pack2(__uint_as_float(rr[i * 8 + 0]) * inv_l, __uint_as_float(rr[i * 8 + 1]) * inv_l);
       u.y = Cvt<T>::pack2(__uint_as_float(rr[i * 8 + 2]) * inv_l, __uint_as_float(rr[i * 8 + 3]) * inv_l);

@@ -49,7 +49,8 @@ def main():
     argv = ['--config_file', cfg_path, '--max-sentences', '4', '--synthetic-data', '--lr', '1e-3', '--no-save',
             '--log-format', 'none', '--distributed-world-size', str(world), '--distributed-rank', str(rank),
             '--device-id', str(local), '--dp-backend', a.backend, '--save-dir', tmp, '--clip-norm', '1.0',
-            '--fast-stat-sync', '--bucket-cap-mb', '1', '--check-params-interval', '1', '--profile-nvtx']
+            '--fast-stat-sync', '--bucket-cap-mb', '1', '--check-params-interval', '1', '--profile-nvtx',
+            '--distributed-timeout', '90']       # a protocol bug must trap within seconds in a test
     if a.optimizer == 'adam':
         argv += ['--adam-betas', '(0.9, 0.98)', '--weight-decay', '0.01']
     if a.cpu:

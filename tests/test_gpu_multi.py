@@ -22,7 +22,7 @@ def _run(tmp_path, nproc, backend, tag, extra=()):
     cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', str(nproc),
            '--master-addr', '127.0.0.1', '--master-port', str(port), WORKER, '--backend', backend, '--out', out,
            '--precision', 'fp16', '--hidden', '256', '--seq', '128', '--steps', '4', *extra]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=420)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-6000:]
     return torch.load(out, weights_only=False)
 
