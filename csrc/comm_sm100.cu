@@ -355,6 +355,125 @@ __device__ __forceinline__ void publish_gather(const UpdArgs& a, int rank, int j
   }
 }
 
+// A CTA hands in the `mine` blocks of gather bucket `cur` it has finished; whoever completes the bucket publishes it.
+__device__ __forceinline__ void hand_in_bucket(const UpdArgs& a, int rank, int cur, unsigned int mine, uint32_t epoch,
+                                               int* sh_flag) {
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const long long lo = static_cast<long long>(cur) * a.blocks_per_gather;
+    const long long hi = lo + a.blocks_per_gather < a.nblocks ? lo + a.blocks_per_gather : a.nblocks;
+    const unsigned int prev = atomicAdd(a.counters + cur, mine);
+    const bool done = prev + mine == static_cast<unsigned int>(hi - lo);
+    if (done) a.counters[cur] = 0;
+    *sh_flag = done ? 1 : 0;
+  }
+  __syncthreads();
+  if (*sh_flag) publish_gather(a, rank, cur, epoch);
+}
+
+// last CTA out clears "an update is waiting"
+__device__ __forceinline__ void clear_pending(const UpdArgs& a, int nblk) {
+  if (a.pending == nullptr) return;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int prev = atomicAdd(a.counters + a.ngather, 1u);
+    if (prev == static_cast<unsigned int>(nblk) - 1) {
+      a.counters[a.ngather] = 0;
+      *a.pending = 0;
+    }
+  }
+}
+
+// Update WITHOUT the gather: Adam / Adadelta on the owned chunks at full speed on the main stream, the new 16-bit
+// values go into this rank's own parameter buffer only. The peers get them from gather_body, which runs next to
+// the following forward pass.
+template <typename OutT, int OPT>
+__device__ __forceinline__ void update_local_body(const UpdArgs& a, int rank, int bid, int nblk) {
+  if (a.scalars[2] != 0.f) return;        // overflow: leave everything untouched
+  const int W = a.W;
+  const float mult = a.scalars[1];
+  const float lr = a.hyper_dev != nullptr ? a.hyper_dev[0] : a.h.lr;
+  const float step_size = lr * (a.hyper_dev != nullptr ? a.hyper_dev[1] : a.h.step_factor);
+  const float decay = 1.0f - a.h.weight_decay * lr;
+  const int vec_per_chunk = a.chunk / 4;
+  const long long stride = static_cast<long long>(W) * a.chunk;
+  OutT* mine_p = reinterpret_cast<OutT*>(a.params.ptr[rank]);
+  for (long long c = bid; c < a.nblocks; c += nblk) {
+    const long long goff = c * stride + static_cast<long long>(rank) * a.chunk;
+    const float4* g4 = reinterpret_cast<const float4*>(a.grad + goff);
+    float4* p4 = reinterpret_cast<float4*>(a.master + c * static_cast<long long>(a.chunk));
+    float4* m4 = reinterpret_cast<float4*>(a.s1 + c * static_cast<long long>(a.chunk));
+    float4* v4 = reinterpret_cast<float4*>(a.s2 + c * static_cast<long long>(a.chunk));
+    for (int i = threadIdx.x; i < vec_per_chunk; i += blockDim.x) {
+      const float4 g = g4[i];
+      const float4 mm = m4[i], vv = v4[i], pp = p4[i];
+      const float gs[4] = {g.x * mult, g.y * mult, g.z * mult, g.w * mult};
+      float s1[4] = {mm.x, mm.y, mm.z, mm.w}, s2[4] = {vv.x, vv.y, vv.z, vv.w}, ps[4] = {pp.x, pp.y, pp.z, pp.w};
+      update4<OPT>(a.h, lr, step_size, decay, gs, ps, s1, s2);
+      m4[i] = make_float4(s1[0], s1[1], s1[2], s1[3]);
+      v4[i] = make_float4(s2[0], s2[1], s2[2], s2[3]);
+      p4[i] = make_float4(ps[0], ps[1], ps[2], ps[3]);
+      uint2 o;
+      o.x = Cvt<OutT>::pack2(ps[0], ps[1]);
+      o.y = Cvt<OutT>::pack2(ps[2], ps[3]);
+      reinterpret_cast<uint2*>(mine_p + goff)[i] = o;
+    }
+  }
+}
+
+// The all-gather on its own: copy this rank's owned 16-bit chunks into every peer's parameter buffer (one
+// multimem.st per vector, or W-1 peer stores), in flat (= forward) order, publishing each gather bucket as soon
+// as it is complete. A pure copy: ~20 registers and no shared memory, so its CTAs fit next to the forward
+// pass's GEMM CTAs, and NVLink -- not the SMs -- sets its pace.
+template <bool MC>
+__device__ __forceinline__ void gather_body(const UpdArgs& a, int rank, int bid, int nblk, uint32_t epoch, int* sh_flag) {
+  const int W = a.W;
+  const bool apply = (a.pending == nullptr || *a.pending != 0) && a.scalars[2] == 0.f;
+  if (!apply) {
+    if (bid == 0)
+      for (int j = 0; j < a.ngather; ++j) publish_gather(a, rank, j, epoch);
+  } else {
+    const int vec_per_chunk = a.chunk / 8;      // uint4 = 8 16-bit parameters
+    const long long stride = static_cast<long long>(W) * a.chunk;
+    const uint16_t* mine_p = reinterpret_cast<const uint16_t*>(a.params.ptr[rank]);
+    int cur = -1;
+    unsigned int mine = 0;
+    for (long long c = bid;; c += nblk) {
+      const int j = c < a.nblocks ? static_cast<int>(c / a.blocks_per_gather) : -2;
+      if (j != cur) {
+        if (cur >= 0) hand_in_bucket(a, rank, cur, mine, epoch, sh_flag);
+        cur = j;
+        mine = 0;
+      }
+      if (j < 0) break;
+      const long long goff = c * stride + static_cast<long long>(rank) * a.chunk;
+      const uint4* src = reinterpret_cast<const uint4*>(mine_p + goff);
+      for (int i = threadIdx.x; i < vec_per_chunk; i += blockDim.x) {
+        const uint4 v = src[i];
+        if constexpr (MC) {
+          asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+                       ::"l"(reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(a.params_mc) + goff) + i),
+                         "f"(__uint_as_float(v.x)), "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)),
+                         "f"(__uint_as_float(v.w))
+                       : "memory");
+        } else {
+#pragma unroll 4
+          for (int p = 1; p < W; ++p) {
+            const int peer = (rank + p) % W;
+            asm volatile("st.relaxed.sys.global.v4.u32 [%0], {%1, %2, %3, %4};"
+                         ::"l"(reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(a.params.ptr[peer]) + goff) + i),
+                           "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+                         : "memory");
+          }
+        }
+      }
+      ++mine;
+    }
+  }
+  clear_pending(a, nblk);
+}
+
 template <typename OutT, int OPT, bool MC>
 __device__ __forceinline__ void update_body(const UpdArgs& a, int rank, int bid, int nblk, uint32_t epoch, int* sh_flag) {
   const int W = a.W;
@@ -375,21 +494,7 @@ __device__ __forceinline__ void update_body(const UpdArgs& a, int rank, int bid,
     for (long long c = bid;; c += nblk) {
       const int j = c < a.nblocks ? static_cast<int>(c / a.blocks_per_gather) : -2;
       if (j != cur) {
-        if (cur >= 0) {
-          // hand in the finished share of bucket `cur`; whoever completes the bucket publishes it
-          __threadfence_system();
-          __syncthreads();
-          if (threadIdx.x == 0) {
-            const long long lo = static_cast<long long>(cur) * a.blocks_per_gather;
-            const long long hi = lo + a.blocks_per_gather < a.nblocks ? lo + a.blocks_per_gather : a.nblocks;
-            const unsigned int prev = atomicAdd(a.counters + cur, mine);
-            const bool done = prev + mine == static_cast<unsigned int>(hi - lo);
-            if (done) a.counters[cur] = 0;
-            *sh_flag = done ? 1 : 0;
-          }
-          __syncthreads();
-          if (*sh_flag) publish_gather(a, rank, cur, epoch);
-        }
+        if (cur >= 0) hand_in_bucket(a, rank, cur, mine, epoch, sh_flag);
         cur = j;
         mine = 0;
       }
@@ -425,17 +530,7 @@ __device__ __forceinline__ void update_body(const UpdArgs& a, int rank, int bid,
       ++mine;
     }
   }
-  // last CTA out clears "an update is waiting"
-  if (a.pending != nullptr) {
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      const unsigned int prev = atomicAdd(a.counters + a.ngather, 1u);
-      if (prev == static_cast<unsigned int>(nblk) - 1) {
-        a.counters[a.ngather] = 0;
-        *a.pending = 0;
-      }
-    }
-  }
+  clear_pending(a, nblk);
 }
 
 template <typename OutT, int OPT, bool MC>
@@ -444,6 +539,20 @@ dp_update_allgather_kernel(UpdArgs a, int rank, uint32_t epoch, const uint32_t* 
   __shared__ int sh_flag;
   if (epoch_dev != nullptr) epoch = *epoch_dev;
   update_body<OutT, OPT, MC>(a, rank, blockIdx.x, gridDim.x, epoch + epoch_offset, &sh_flag);
+}
+
+template <typename OutT, int OPT>
+__global__ void __launch_bounds__(256)
+dp_update_local_kernel(UpdArgs a, int rank) {
+  update_local_body<OutT, OPT>(a, rank, blockIdx.x, gridDim.x);
+}
+
+template <bool MC>
+__global__ void __launch_bounds__(RS_THREADS, 6)
+dp_allgather_kernel(UpdArgs a, int rank, uint32_t epoch, const uint32_t* __restrict__ epoch_dev, int epoch_offset) {
+  __shared__ int sh_flag;
+  if (epoch_dev != nullptr) epoch = *epoch_dev;
+  gather_body<MC>(a, rank, blockIdx.x, gridDim.x, epoch + epoch_offset, &sh_flag);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -479,7 +588,7 @@ struct EmuRank {
 struct EmuArgs {
   EmuRank r[DP_MAX_WORLD];
   PeerTable grads, params, sigs;
-  int W, G, chunk, nbuckets, ngather, opt;
+  int W, G, chunk, nbuckets, ngather, opt, split;
   long long total_chunks, chunks_per_bucket, nblocks, blocks_per_gather;
   NormArgs norm;
   DpHyper h;
@@ -527,8 +636,17 @@ dp_emulate_kernel(EmuArgs e) {
   u.params = e.params; u.sigs = e.sigs; u.params_mc = nullptr;
   u.W = e.W; u.chunk = e.chunk; u.ngather = e.ngather; u.nblocks = e.nblocks; u.blocks_per_gather = e.blocks_per_gather;
   u.h = e.h; u.scalars = me.scalars; u.hyper_dev = e.hyper_dev; u.counters = me.counters; u.pending = me.pending;
-  if (e.opt == DP_OPT_ADAM) update_body<OutT, DP_OPT_ADAM, false>(u, rank, bid, e.G, e.epoch, &sh_flag);
-  else update_body<OutT, DP_OPT_ADADELTA, false>(u, rank, bid, e.G, e.epoch, &sh_flag);
+  if (e.split) {
+    // the production sequence: update at the end of the step, gather next to the following forward pass
+    if (e.opt == DP_OPT_ADAM) update_local_body<OutT, DP_OPT_ADAM>(u, rank, bid, e.G);
+    else update_local_body<OutT, DP_OPT_ADADELTA>(u, rank, bid, e.G);
+    rank_barrier(bar, 3 * e.G);
+    gather_body<false>(u, rank, bid, e.G, e.epoch, &sh_flag);
+  } else if (e.opt == DP_OPT_ADAM) {
+    update_body<OutT, DP_OPT_ADAM, false>(u, rank, bid, e.G, e.epoch, &sh_flag);
+  } else {
+    update_body<OutT, DP_OPT_ADADELTA, false>(u, rank, bid, e.G, e.epoch, &sh_flag);
+  }
   if (bid == 0) wait_params_body(e.sigs, rank, e.W, 0, e.ngather - 1, e.epoch);
 }
 
@@ -660,6 +778,59 @@ extern "C" int hs_dp_update_allgather(int opt, const float* grad, float* master,
   return post_launch("dp_update_allgather_kernel");
 }
 
+// Adam / Adadelta on the owned chunks only (no stores to peers, no flags): the end-of-step half of the split update.
+extern "C" int hs_dp_update_local(int opt, const float* grad, float* master, float* state1, float* state2,
+                                  void* param_local, int rank, int W, long long nblocks, int chunk, int out_dtype,
+                                  float lr, float a_coef, float b_coef, float eps, float weight_decay, float step_factor,
+                                  const float* scalars, const float* hyper_dev, int grid_blocks, hs_stream_t stream) {
+  UpdArgs a;
+  memset(&a, 0, sizeof(a));
+  if (chunk % 4 != 0 || nblocks <= 0 || rank < 0 || rank >= W || W > DP_MAX_WORLD || (opt != DP_OPT_ADAM && opt != DP_OPT_ADADELTA)) {
+    set_last_error("hs_dp_update_local: bad arguments (chunk=%d nblocks=%lld rank=%d W=%d opt=%d)", chunk, nblocks, rank, W, opt);
+    return 1;
+  }
+  a.grad = grad; a.master = master; a.s1 = state1; a.s2 = state2;
+  a.params.ptr[rank] = param_local;
+  a.W = W; a.chunk = chunk; a.nblocks = nblocks;
+  a.h = DpHyper{lr, a_coef, b_coef, eps, weight_decay, step_factor};
+  a.scalars = scalars; a.hyper_dev = hyper_dev;
+  int grid = grid_blocks > 0 ? grid_blocks : num_sms() * 8;
+  if (grid > nblocks) grid = static_cast<int>(nblocks);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (out_dtype == HS_F16) {
+    if (opt == DP_OPT_ADAM) dp_update_local_kernel<__half, DP_OPT_ADAM><<<grid, 256, 0, st>>>(a, rank);
+    else dp_update_local_kernel<__half, DP_OPT_ADADELTA><<<grid, 256, 0, st>>>(a, rank);
+  } else if (out_dtype == HS_BF16) {
+    if (opt == DP_OPT_ADAM) dp_update_local_kernel<__nv_bfloat16, DP_OPT_ADAM><<<grid, 256, 0, st>>>(a, rank);
+    else dp_update_local_kernel<__nv_bfloat16, DP_OPT_ADADELTA><<<grid, 256, 0, st>>>(a, rank);
+  } else { set_last_error("hs_dp_update_local: parameters must be f16 or bf16"); return 1; }
+  return post_launch("dp_update_local_kernel");
+}
+
+// The gather half: this rank's owned 16-bit chunks go to every peer, one arrival flag per gather bucket.
+extern "C" int hs_dp_allgather(void* const* param_ptrs, void* params_mc, void* const* sig_ptrs, int rank, int W,
+                               long long nblocks, int chunk, const float* scalars, unsigned epoch,
+                               const unsigned* epoch_dev, int epoch_offset, unsigned int* counters, int* pending,
+                               int ngather, int grid_blocks, hs_stream_t stream) {
+  UpdArgs a;
+  memset(&a, 0, sizeof(a));
+  if (fill_table(&a.params, param_ptrs, W) || fill_table(&a.sigs, sig_ptrs, W)) return 1;
+  if (chunk % 8 != 0 || nblocks <= 0 || ngather < 1 || ngather > DP_MAX_GATHER) {
+    set_last_error("hs_dp_allgather: bad layout (chunk=%d nblocks=%lld ngather=%d)", chunk, nblocks, ngather);
+    return 1;
+  }
+  a.params_mc = params_mc;
+  a.W = W; a.chunk = chunk; a.ngather = gather_count(nblocks, ngather); a.nblocks = nblocks;
+  a.blocks_per_gather = gather_blocks(nblocks, ngather);
+  a.scalars = scalars; a.counters = counters; a.pending = pending;
+  int grid = grid_blocks > 0 ? grid_blocks : num_sms();
+  if (grid > nblocks) grid = static_cast<int>(nblocks);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (params_mc != nullptr) dp_allgather_kernel<true><<<grid, RS_THREADS, 0, st>>>(a, rank, epoch, epoch_dev, epoch_offset);
+  else dp_allgather_kernel<false><<<grid, RS_THREADS, 0, st>>>(a, rank, epoch, epoch_dev, epoch_offset);
+  return post_launch("dp_allgather_kernel");
+}
+
 extern "C" int hs_dp_gather_bucket_of(long long nblocks, int ngather, long long block) {
   const long long bpg = gather_blocks(nblocks, ngather);
   const int n = gather_count(nblocks, ngather);
@@ -690,7 +861,7 @@ extern "C" int hs_dp_emulate_step(int W, int blocks_per_rank, void* const* grad_
                                   unsigned int* barrier_words, long long total_chunks, long long chunks_per_bucket,
                                   int chunk, int ngather, int opt, int out_dtype, float lr, float a_coef, float b_coef,
                                   float eps, float weight_decay, float step_factor, float mult_host, float max_norm,
-                                  unsigned epoch, hs_stream_t stream) {
+                                  unsigned epoch, int split, hs_stream_t stream) {
   EmuArgs e;
   memset(&e, 0, sizeof(e));
   if (fill_table(&e.grads, grad_ptrs, W) || fill_table(&e.params, param_ptrs, W) || fill_table(&e.sigs, sig_ptrs, W)) return 1;
@@ -700,7 +871,7 @@ extern "C" int hs_dp_emulate_step(int W, int blocks_per_rank, void* const* grad_
   }
   for (int r = 0; r < W; ++r)
     e.r[r] = EmuRank{sumsq[r], sample_size ? sample_size[r] : nullptr, scalars[r], skip[r], master[r], state1[r], state2[r], counters[r], pending ? pending[r] : nullptr};
-  e.W = W; e.G = blocks_per_rank; e.chunk = chunk; e.ngather = ngather; e.opt = opt;
+  e.W = W; e.G = blocks_per_rank; e.chunk = chunk; e.ngather = ngather; e.opt = opt; e.split = split;
   e.total_chunks = total_chunks; e.chunks_per_bucket = chunks_per_bucket;
   e.nbuckets = static_cast<int>((total_chunks + chunks_per_bucket - 1) / chunks_per_bucket);
   e.nblocks = total_chunks / W; e.blocks_per_gather = gather_blocks(e.nblocks, ngather);

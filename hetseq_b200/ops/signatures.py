@@ -30,11 +30,13 @@ SIGNATURES = {
     'hs_dp_norm_exchange': [vp, ci, ci, cu, vp, vp, cf, vp, vp, cf, vp, vp, vp, vp],
     'hs_dp_update_allgather': [ci, vp, vp, vp, vp, vp, vp, vp, ci, ci, cl, ci, ci, cf, cf, cf, cf, cf, cf, vp, vp, cu,
                                vp, ci, vp, vp, ci, ci, vp],
+    'hs_dp_update_local': [ci, vp, vp, vp, vp, vp, ci, ci, cl, ci, ci, cf, cf, cf, cf, cf, cf, vp, vp, ci, vp],
+    'hs_dp_allgather': [vp, vp, vp, ci, ci, cl, ci, vp, cu, vp, ci, vp, vp, ci, ci, vp],
     'hs_dp_gather_bucket_of': [cl, ci, cl],
     'hs_dp_gather_count': [cl, ci],
     'hs_dp_wait_params': [vp, ci, ci, ci, ci, cu, vp, ci, vp],
     'hs_dp_emulate_step': [ci, ci, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, cl, cl, ci, ci, ci, ci,
-                           cf, cf, cf, cf, cf, cf, cf, cf, cu, vp],
+                           cf, cf, cf, cf, cf, cf, cf, cf, cu, ci, vp],
     'hs_sumsq_noalloc': [vp, ci, cl, ci, cl, vp, ci, vp],
     'hs_adadelta_flat': [vp, vp, vp, vp, vp, ci, cl, ci, cl, cf, cf, cf, cf, cf, vp, vp, vp, vp],
 }

@@ -244,7 +244,11 @@ class FusedBackend(AllReduceBackend):
         rb = int(os.environ.get('HETSEQ_RS_BLOCKS', '0') or getattr(args, 'fused_rs_blocks', 0) or default_rb)
         self.rs_blocks = 0 if rb < 0 else rb
         self.update_blocks = int(os.environ.get('HETSEQ_UPDATE_BLOCKS', '0') or 0)
+        self.gather_blocks = int(os.environ.get('HETSEQ_GATHER_BLOCKS', '0') or 0)
         self.overlap_update = os.environ.get('HETSEQ_DP_ROTATE', '1') != '0'
+        # split: Adam / Adadelta at the end of the step at full speed, only the gather rides next to the forward
+        # pass (a pure copy fits beside the GEMM CTAs; the full update does not get enough of an SM there)
+        self.split_update = os.environ.get('HETSEQ_DP_SPLIT', '1') != '0'
         self._opt = None            # the optimizer whose state the update kernel works on (bind_optimizer)
         self._joined = True
         self._gated = self.ngather  # gather buckets already waited for in this update (all: nothing outstanding)
@@ -273,15 +277,7 @@ class FusedBackend(AllReduceBackend):
     def bind_optimizer(self, opt):
         self._opt = opt
 
-    def _launch_update(self, epoch_offset: int, flush: bool):
-        """The update kernel applies whatever the device-side ``pending`` word says is waiting (nothing on the
-        first step or right after a flush) and publishes this epoch's parameter flags either way. In-step it
-        reads the PREVIOUS step's [lr, step factor] (``hyper_prev_t``), from ``flush`` the current ones."""
-        opt = self._opt
-        if opt is None:
-            raise RuntimeError('fused backend: no optimizer bound (bind_optimizer)')
-        main = torch.cuda.current_stream()
-        self.update_stream.wait_stream(main)
+    def _opt_args(self, opt):
         h = opt.hyper
         kind = OPT_KIND[opt.kind]
         if kind == 0:
@@ -290,11 +286,34 @@ class FusedBackend(AllReduceBackend):
         else:
             a, b = h['rho'], 0.0
             s1, s2 = opt.state['square_avg'], opt.state['acc_delta']
+        return kind, float(a), float(b), s1, s2
+
+    def _launch_update(self, epoch_offset: int, flush: bool):
+        """Side-stream half of the update. Split mode (default): the all-gather of this rank's freshly updated
+        chunks (``hs_dp_allgather``; the Adam / Adadelta math already ran at the end of the previous step). Fused
+        mode (``HETSEQ_DP_SPLIT=0``): update and gather in one kernel, which then reads the PREVIOUS step's
+        [lr, step factor] (``hyper_prev_t``) in-step and the current ones from ``flush``. Either kernel acts only
+        if the device-side ``pending`` word says something is waiting (nothing on the first step or right after
+        a flush) and publishes this epoch's parameter flags in any case."""
+        opt = self._opt
+        if opt is None:
+            raise RuntimeError('fused backend: no optimizer bound (bind_optimizer)')
+        main = torch.cuda.current_stream()
+        self.update_stream.wait_stream(main)
         buf = self.buffer
+        if self.split_update:
+            lib.check(self.L.hs_dp_allgather(
+                self.param_ptrs, self.param_mc, self.sig_ptrs, self.rank, self.world_size, buf.num_blocks, CHUNK,
+                self.scalars.data_ptr(), 0, self.epoch_t.data_ptr(), int(epoch_offset), self.counters.data_ptr(),
+                self.pending_dev.data_ptr(), self.ngather_req, self.gather_blocks, self.update_stream.cuda_stream),
+                'hs_dp_allgather')
+            return
+        h = opt.hyper
+        kind, a, b, s1, s2 = self._opt_args(opt)
         lib.check(self.L.hs_dp_update_allgather(
             kind, buf.flat_grad.data_ptr(), opt.master.data_ptr(), s1.data_ptr(), s2.data_ptr(), self.param_ptrs,
             self.param_mc, self.sig_ptrs, self.rank, self.world_size, buf.num_blocks, CHUNK,
-            lib.dtype_code(buf.param_dtype), float(h['lr']), float(a), float(b), float(h['eps']),
+            lib.dtype_code(buf.param_dtype), float(h['lr']), a, b, float(h['eps']),
             float(h['weight_decay']), 1.0, self.scalars.data_ptr(),
             (opt.hyper_t if flush else opt.hyper_prev_t).data_ptr(), 0,
             self.epoch_t.data_ptr(), int(epoch_offset), self.counters.data_ptr(), self.pending_dev.data_ptr(),
@@ -364,21 +383,37 @@ class FusedBackend(AllReduceBackend):
         return self.scalars[0]
 
     def queue_update(self, opt):
-        """The update of this step is applied at the start of the next one (or by ``flush``)."""
+        """Split mode: run the update on the owned chunks now (main stream) and leave the gather to the start of
+        the next step; fused mode: leave both. ``flush`` brings either forward."""
         self._opt = opt
+        if self.split_update:
+            h = opt.hyper
+            kind, a, b, s1, s2 = self._opt_args(opt)
+            buf = self.buffer
+            lib.check(self.L.hs_dp_update_local(
+                kind, buf.flat_grad.data_ptr(), opt.master.data_ptr(), s1.data_ptr(), s2.data_ptr(),
+                buf.flat_param.data_ptr(), self.rank, self.world_size, buf.num_blocks, CHUNK,
+                lib.dtype_code(buf.param_dtype), float(h['lr']), a, b, float(h['eps']), float(h['weight_decay']), 1.0,
+                self.scalars.data_ptr(), opt.hyper_t.data_ptr(), self.update_blocks, lib.stream_ptr()),
+                'hs_dp_update_local')
         if not self.overlap_update:
-            self.flush(sync=False)
+            self._apply_pending()
 
-    def flush(self, sync: bool = True):
-        """Apply a pending update now and wait until every rank's parameters have arrived. Collective in
-        effect (every rank reaches the same call sites: checkpoints, validation, consistency checks, close)."""
-        if self._opt is None or self._capturing():
-            return
+    def _apply_pending(self):
+        """Bring the pending gather (fused mode: update + gather) forward and wait for every rank's parameters;
+        stream-ordered only, so it is safe inside a graph capture."""
         self._launch_update(epoch_offset=1, flush=True)
         lib.check(self.L.hs_dp_wait_params(self.sig_ptrs, self.rank, self.world_size, 0, self.ngather - 1, 0,
                                            self.epoch_t.data_ptr(), 1, self.update_stream.cuda_stream),
                   'hs_dp_wait_params')
         torch.cuda.current_stream().wait_stream(self.update_stream)
+
+    def flush(self, sync: bool = True):
+        """Make a pending update visible now and wait until every rank's parameters have arrived. Collective in
+        effect (every rank reaches the same call sites: checkpoints, validation, consistency checks, close)."""
+        if self._opt is None or self._capturing():
+            return
+        self._apply_pending()
         if sync:
             torch.cuda.current_stream().synchronize()
 

@@ -251,6 +251,19 @@ HS_API int hs_dp_update_allgather(int opt, const float* grad, float* master, flo
                                   const float* hyper_dev, unsigned epoch, const unsigned* epoch_dev, int epoch_offset,
                                   unsigned int* counters, int* pending, int ngather, int grid_blocks,
                                   hs_stream_t stream);
+/* The same update split in two, which is what training uses: hs_dp_update_local runs Adam / Adadelta on the owned
+ * chunks at the end of the step and stores the new 16-bit values into THIS rank's parameter buffer only;
+ * hs_dp_allgather later copies the owned chunks into every peer's buffer (multimem.st or W-1 peer stores), gather
+ * bucket by gather bucket with the same flags, counters and `pending` protocol as hs_dp_update_allgather. The
+ * gather is a pure copy that fits next to the next forward pass's GEMMs, where it is overlapped. */
+HS_API int hs_dp_update_local(int opt, const float* grad, float* master, float* state1, float* state2,
+                              void* param_local, int rank, int W, long long nblocks, int chunk, int out_dtype,
+                              float lr, float a_coef, float b_coef, float eps, float weight_decay, float step_factor,
+                              const float* scalars, const float* hyper_dev, int grid_blocks, hs_stream_t stream);
+HS_API int hs_dp_allgather(void* const* param_ptrs, void* params_mc, void* const* sig_ptrs, int rank, int W,
+                           long long nblocks, int chunk, const float* scalars, unsigned epoch,
+                           const unsigned* epoch_dev, int epoch_offset, unsigned int* counters, int* pending,
+                           int ngather, int grid_blocks, hs_stream_t stream);
 /* Gather bucket that owned block `block` (of nblocks per rank) falls into, and the number of non-empty gather
  * buckets (<= ngather: buckets hold ceil(nblocks / ngather) blocks each, so the last requested ones may be
  * empty; flags exist, and may be waited for, only for buckets [0, hs_dp_gather_count)). */
@@ -262,7 +275,8 @@ HS_API int hs_dp_wait_params(void* const* sig_ptrs, int rank, int W, int j_lo, i
                              const unsigned* epoch_dev, int epoch_offset, hs_stream_t stream);
 /* Protocol test on ONE GPU: W virtual ranks (blocks_per_rank CTAs each) run one whole update -- the same device
  * code as the four kernels above, peer-load / peer-store variant -- inside one cooperative launch. All pointer
- * arguments are host arrays of W device pointers (one "rank" each); barrier_words: W words. */
+ * arguments are host arrays of W device pointers (one "rank" each); barrier_words: W words. split = 1 runs
+ * hs_dp_update_local + hs_dp_allgather instead of the fused hs_dp_update_allgather. */
 HS_API int hs_dp_emulate_step(int W, int blocks_per_rank, void* const* grad_ptrs, void* const* param_ptrs,
                               void* const* sig_ptrs, float* const* sumsq, const float* const* sample_size,
                               float* const* scalars, int* const* skip, float* const* master, float* const* state1,
@@ -270,7 +284,7 @@ HS_API int hs_dp_emulate_step(int W, int blocks_per_rank, void* const* grad_ptrs
                               unsigned int* barrier_words, long long total_chunks, long long chunks_per_bucket,
                               int chunk, int ngather, int opt, int out_dtype, float lr, float a_coef, float b_coef,
                               float eps, float weight_decay, float step_factor, float mult_host, float max_norm,
-                              unsigned epoch, hs_stream_t stream);
+                              unsigned epoch, int split, hs_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -81,7 +81,7 @@ class VirtualRanks(object):
                                        weight_decay=self.hyper['weight_decay'])
         self.t = 0
 
-    def step(self, grads, sample_sizes, mult_host=1.0, max_norm=1.0, chunks_per_bucket=3, blocks_per_rank=3):
+    def step(self, grads, sample_sizes, mult_host=1.0, max_norm=1.0, chunks_per_bucket=3, blocks_per_rank=3, split=1):
         import math
         W = self.W
         for r in range(W):
@@ -98,7 +98,7 @@ class VirtualRanks(object):
             _ptr_array(self.master), _ptr_array(self.s1), _ptr_array(self.s2), _ptr_array(self.counters),
             _ptr_array(self.pending), self.barrier.data_ptr(), W * self.blocks, chunks_per_bucket, CHUNK, self.ngather_req,
             0 if self.opt == 'adam' else 1, self.lib.dtype_code(self.dtype), self.hyper['lr'], a, b, self.hyper['eps'],
-            self.hyper['weight_decay'], step_factor, mult_host, max_norm, self.epoch, self.lib.stream_ptr())
+            self.hyper['weight_decay'], step_factor, mult_host, max_norm, self.epoch, int(split), self.lib.stream_ptr())
         self.lib.check(rc, 'hs_dp_emulate_step')
         torch.cuda.synchronize()
         # ---- oracle ------------------------------------------------------------------------------------
@@ -148,7 +148,7 @@ def test_virtual_ranks_match_reference_update(W, dtype, opt):
         if it == 1:
             sizes[0] = 0
         gsum, norm, bad = vr.step(grads, sizes, mult_host=1.0 / 128.0, max_norm=0.05 if it != 2 else 0.0,
-                                  chunks_per_bucket=3 + it, blocks_per_rank=1 + 2 * it)
+                                  chunks_per_bucket=3 + it, blocks_per_rank=1 + 2 * it, split=it % 2 == 0)
         assert not bad
         _check(vr, gsum, norm, bad)
 
