@@ -159,6 +159,12 @@ def add_distributed_training_args(parser):
                             "all-reduce + replicated optimizer (the baseline); 'sharded': the fused protocol "
                             "emulated with torch.distributed collectives (CPU tests); 'auto': fused when "
                             "the ranks share one NVLink domain and CUDA, else nccl")
+    group.add_argument('--fused-transport', default='auto', choices=['auto', 'multimem', 'p2p'],
+                       help="how the fused gradient path moves data: 'multimem' = NVLS (multimem.ld_reduce / multimem.st "
+                            "through the NVSwitch), 'p2p' = peer loads / stores; 'auto' = multimem from 4 GPUs on when "
+                            "the symmetric buffers have a multicast mapping")
+    group.add_argument('--fused-rs-blocks', default=0, type=int, metavar='N',
+                       help='CTAs of a reduce-scatter launch of the fused gradient path (0 = chosen by world size)')
     group.add_argument('--bucket-cap-mb', default=25, type=int, metavar='MB',
                        help='bucket size for reduction')
     group.add_argument('--fix-batches-to-gpus', action='store_true',
@@ -168,7 +174,8 @@ def add_distributed_training_args(parser):
     group.add_argument('--fast-stat-sync', default=False, action='store_true',
                        help='sync the fixed set of stats with one 6-element all-reduce')
     group.add_argument('--distributed-timeout', default=1800, type=int, metavar='SEC',
-                       help='process-group timeout in seconds')
+                       help='process-group timeout in seconds; also bounds every in-kernel wait on a peer of the '
+                            'fused gradient path (beyond it the kernel reports the peer and traps)')
     return group
 
 

@@ -12,13 +12,20 @@ run() {   # label, env assignments..., then "--" and extra args
       --master-port $((29600 + RANDOM % 300)) bench.py --gpus $N --steps 20 --warmup 6 --no-e2e --no-dp-check "$@" 2>&1 \
       | grep -E '^\{"metric"|Error|error' | tail -2 >> $OUT
 }
-run "default (split update, gather overlapped, multimem)" X=1 -- "$@"
-run "peer loads/stores instead of multimem" HETSEQ_DP_TRANSPORT=p2p -- "$@"
-run "fused update+gather kernel rotated into the forward" HETSEQ_DP_SPLIT=0 -- "$@"
-run "gather not overlapped (applied at the end of the step)" HETSEQ_DP_ROTATE=0 -- "$@"
-run "reduce-scatter with 74 CTAs" HETSEQ_RS_BLOCKS=74 -- "$@"
-run "reduce-scatter with 296 CTAs" HETSEQ_RS_BLOCKS=296 -- "$@"
-run "NCCL all-reduce backend (eager)" X=1 -- --dp-backend nccl "$@"
+# VARIANTS picks a subset (default: all)
+V=${VARIANTS:-"default p2p multimem fusedupd norotate rs74 rs296 nccl"}
+for v in $V; do
+  case $v in
+    default)  run "default (split update, gather overlapped, transport auto)" X=1 -- "$@" ;;
+    p2p)      run "peer loads/stores" HETSEQ_DP_TRANSPORT=p2p -- "$@" ;;
+    multimem) run "multimem (NVLS) loads/stores" HETSEQ_DP_TRANSPORT=multimem -- "$@" ;;
+    fusedupd) run "fused update+gather kernel rotated into the forward" HETSEQ_DP_SPLIT=0 -- "$@" ;;
+    norotate) run "gather not overlapped (applied at the end of the step)" HETSEQ_DP_ROTATE=0 -- "$@" ;;
+    rs74)     run "reduce-scatter with 74 CTAs" HETSEQ_RS_BLOCKS=74 -- "$@" ;;
+    rs296)    run "reduce-scatter with 296 CTAs" HETSEQ_RS_BLOCKS=296 -- "$@" ;;
+    nccl)     run "NCCL all-reduce backend (eager)" X=1 -- --dp-backend nccl "$@" ;;
+  esac
+done
 python - <<'PY' $OUT
 import json, sys
 for line in open(sys.argv[1]):
