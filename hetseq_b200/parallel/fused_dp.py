@@ -240,15 +240,20 @@ class FusedBackend(AllReduceBackend):
         # the update number lives in device memory and is bumped by a tiny device op per update, so the
         # very same kernel arguments stay valid when the step is replayed from a CUDA graph
         self.epoch_t = torch.zeros(1, dtype=torch.int32, device=dev)
-        # reduce-scatter grid. Peer loads: 2 CTAs per SM measured best next to backward on 8 GPUs (14.2 ms/step
-        # vs 14.7 with 148 and 15.4 with one CTA per chunk), 148 on 2 GPUs. Switch-side reduction needs one
-        # request per vector instead of W-1, so half the CTAs cover the latency.
-        # HETSEQ_RS_BLOCKS pins another size, -1 = one CTA per owned chunk
-        default_rb = 148 if (W <= 2 or self.transport == 'multimem') else 296
+        # Grids of the kernels that run NEXT TO forward / backward: the fewer CTAs cover the NVLink latency, the
+        # less they take from the GEMMs. Measured (bench.py, BERT-large, graph): 8 GPUs multimem, reduce-scatter
+        # CTAs 148 / 74 / 37 -> 14.38 / 13.56 / 13.46 ms per step, gather 148 -> 37 CTAs another -0.4 ms (13.15);
+        # peer loads need (W-1) x more requests in flight: 2 GPUs 148 / 74 / 37 CTAs -> 14.46 / 14.48 / 15.63 ms,
+        # 8 GPUs 296 CTAs 14.56 ms. HETSEQ_RS_BLOCKS / HETSEQ_GATHER_BLOCKS pin other sizes (RS: -1 = one CTA per
+        # owned chunk).
+        if self.transport == 'multimem':
+            default_rb, default_gb = 74, 37
+        else:
+            default_rb, default_gb = (148 if W <= 2 else 296), 148
         rb = int(os.environ.get('HETSEQ_RS_BLOCKS', '0') or getattr(args, 'fused_rs_blocks', 0) or default_rb)
         self.rs_blocks = 0 if rb < 0 else rb
         self.update_blocks = int(os.environ.get('HETSEQ_UPDATE_BLOCKS', '0') or 0)
-        self.gather_blocks = int(os.environ.get('HETSEQ_GATHER_BLOCKS', '0') or 0)
+        self.gather_blocks = int(os.environ.get('HETSEQ_GATHER_BLOCKS', '0') or default_gb)
         self.overlap_update = os.environ.get('HETSEQ_DP_ROTATE', '1') != '0'
         # split: Adam / Adadelta at the end of the step at full speed, only the gather rides next to the forward
         # pass (a pure copy fits beside the GEMM CTAs; the full update does not get enough of an SM there)

@@ -22,6 +22,10 @@ for v in $V; do
     fusedupd) run "fused update+gather kernel rotated into the forward" HETSEQ_DP_SPLIT=0 -- "$@" ;;
     norotate) run "gather not overlapped (applied at the end of the step)" HETSEQ_DP_ROTATE=0 -- "$@" ;;
     rs74)     run "reduce-scatter with 74 CTAs" HETSEQ_RS_BLOCKS=74 -- "$@" ;;
+    rs37)     run "reduce-scatter with 37 CTAs" HETSEQ_RS_BLOCKS=37 -- "$@" ;;
+    rs74g37)  run "reduce-scatter with 74 CTAs, gather with 37" HETSEQ_RS_BLOCKS=74 HETSEQ_GATHER_BLOCKS=37 -- "$@" ;;
+    rs74g74)  run "reduce-scatter with 74 CTAs, gather with 74" HETSEQ_RS_BLOCKS=74 HETSEQ_GATHER_BLOCKS=74 -- "$@" ;;
+    env:*)    IFS=, read -ra kv <<< "${v#env:}"; run "$v" "${kv[@]}" -- "$@" ;;
     rs296)    run "reduce-scatter with 296 CTAs" HETSEQ_RS_BLOCKS=296 -- "$@" ;;
     nccl)     run "NCCL all-reduce backend (eager)" X=1 -- --dp-backend nccl "$@" ;;
   esac
