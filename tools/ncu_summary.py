@@ -62,31 +62,43 @@ def fmt(v, unit):
     return ('%d' % x) if x == int(x) else '%.3g' % x
 
 
+def short_name(full):
+    name = full.replace('(anonymous namespace)::', '').replace('hs::', '').replace('void ', '')
+    i = name.find('(')
+    return name[:i] if i > 0 else name
+
+
 def section(rep):
     header, units, data = raw_page(rep)
     col = {name: i for i, name in enumerate(header)}
-    out = ['## `%s`' % os.path.basename(rep), '']
-    for r in data[:1]:      # the captured launches of one family are alike: the first one is tabulated
-        out.append('kernel: `%s`' % r[col['Kernel Name']][:160])
-        out += ['', '| metric | value |', '| --- | --- |']
+    groups = {}
+    for r in data:                       # launches of the same kernel instance are alike: tabulate the first,
+        groups.setdefault(short_name(r[col['Kernel Name']]), []).append(r)       # list the durations of all
+    out = []
+    tcol = col['gpu__time_duration.sum']
+    for name, rows in groups.items():
+        r = rows[0]
+        out += ['## `%s`' % name[:150], '', 'from `%s`, %d launches captured' % (os.path.basename(rep), len(rows)), '',
+                '| metric | value |', '| --- | --- |']
         for key, label in WANT:
             if key in col:
                 out.append('| %s (`%s`) | %s |' % (label, key, fmt(r[col[key]], units[col[key]])))
         stalls = []
-        for name, i in col.items():
-            if name.startswith(STALL_PREFIX) and name.endswith(STALL_SUFFIX) and 'not_issued' not in name:
+        for cname, i in col.items():
+            if cname.startswith(STALL_PREFIX) and cname.endswith(STALL_SUFFIX) and 'not_issued' not in cname:
                 try:
-                    stalls.append((float(r[i].replace(',', '')), name[len(STALL_PREFIX):-len(STALL_SUFFIX)]))
+                    stalls.append((float(r[i].replace(',', '')), cname[len(STALL_PREFIX):-len(STALL_SUFFIX)]))
                 except ValueError:
                     pass
         stalls.sort(reverse=True)
         if stalls:
             out += ['', 'top warp-stall reasons (warps stalled per issue-active cycle): ' +
                     ', '.join('%s %.2f' % (n, v) for v, n in stalls[:5])]
-    if len(data) > 1:
-        times = [fmt(r[col['gpu__time_duration.sum']], units[col['gpu__time_duration.sum']]) for r in data]
-        out += ['', 'all captured launches: ' + ', '.join(times)]
-    return '\n'.join(out) + '\n'
+        if len(rows) > 1:
+            out += ['', 'durations of the captured launches: ' + ', '.join(fmt(x[tcol], units[tcol]) for x in rows[:12]) +
+                    (' ...' if len(rows) > 12 else '')]
+        out.append('')
+    return '\n'.join(out)
 
 
 def main():
