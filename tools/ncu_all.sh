@@ -22,4 +22,6 @@ cap misc 'xent_|embed_|adam_flat|sumsq_|gather_rows|scatter_add_rows|colsum|sum_
 cap gemm 'gemm_tcgen05' 1200 14
 python tools/ncu_summary.py gpurun_out/ncu_fwd.ncu-rep gpurun_out/ncu_bwd.ncu-rep gpurun_out/ncu_misc.ncu-rep \
     gpurun_out/ncu_gemm.ncu-rep > gpurun_out/ncu_kernels.md || true
+# gpurun brings back at most 64 MiB: the summary is what gets committed; keep only the two small reports
 ls -la gpurun_out/ncu_*
+rm -f gpurun_out/ncu_gemm.ncu-rep gpurun_out/ncu_misc.ncu-rep
