@@ -59,6 +59,8 @@ def fmt(v, unit):
         return '%.1f us' % x
     if unit == '%':
         return '%.1f %%' % x
+    if unit in ('us', 'ns', 'ms', 's', 'KB', 'MB', 'GB', 'B', 'Kbyte/block', 'byte/block', 'Kbyte'):
+        return '%.4g %s' % (x, unit)
     return ('%d' % x) if x == int(x) else '%.3g' % x
 
 
