@@ -237,10 +237,28 @@ def run_ours(a):
 
     # kernels of ours per update: counted on one eager update (a CUDA-graph replay re-issues exactly the
     # kernels that were captured, without going through the launchers' counter)
+    step_device(dev[0])          # first update: lazy initialisation, not counted
+    torch.cuda.synchronize()
+    prof = None
+    try:                         # every kernel of one eager update, whoever launched it (CUPTI)
+        from torch.profiler import ProfilerActivity, profile
+        prof = profile(activities=[ProfilerActivity.CUDA])
+        prof.__enter__()
+    except Exception:            # noqa: BLE001 -- no profiler: only the library's own counter is reported
+        prof = None
     c0 = lib.launch_count() if lib.available() else 0
-    step_device(dev[0])
+    step_device(dev[1 % len(dev)])
     torch.cuda.synchronize()
     launches_per_step = (lib.launch_count() - c0) if lib.available() else 0
+    other_launches = None
+    if prof is not None:
+        try:
+            prof.__exit__(None, None, None)
+            total = sum(int(k.count) for k in prof.key_averages()
+                        if k.device_time_total > 0 and 'Memcpy' not in k.key and 'Memset' not in k.key)
+            other_launches = max(0, total - int(launches_per_step))
+        except Exception:        # noqa: BLE001
+            other_launches = None
 
     e2e_first = os.environ.get('HETSEQ_BENCH_E2E_FIRST', '0') == '1' and not a.no_e2e
     if e2e_first:      # diagnosis: does the order of the two timed loops matter (power / thermal state)?
@@ -312,6 +330,8 @@ def run_ours(a):
             'clocks': sampler.summary() if sampler else None,
             'gpu_launches': launches_timed, 'gpu_launches_per_step': launches_per_step,
             'overflow_steps': int(overflow_timed),
+            # kernels of one eager update that are NOT this library's (ATen elementwise / reductions / copies, NCCL)
+            'other_kernel_launches_per_step': other_launches,
         }
         if dp_check is not None:
             out['dp_check'] = dp_check

@@ -72,8 +72,10 @@ class LinearFn(torch.autograd.Function):
         ldx = ldx or K
         ldy = ldy_pad or N
         y = torch.empty(M, ldy, dtype=x.dtype, device=x.device)
+        # GELU: the epilogue also emits gelu'(pre-activation) (they share the erf), so backward is one multiply
         aux = torch.empty(M, N, dtype=x.dtype, device=x.device) if act == ACT_GELU else None
-        native.gemm(x, weight, y, M, N, K, lda=ldx, ldb=K, ldc=ldy, bias=bias, act=act, aux_out=aux, ldaux=N)
+        native.gemm(x, weight, y, M, N, K, lda=ldx, ldb=K, ldc=ldy, bias=bias,
+                    act=ACT_GELU_DAUX if act == ACT_GELU else act, aux_out=aux, ldaux=N)
         ctx.save_for_backward(x, weight, aux if aux is not None else (y if act == ACT_TANH else None))
         ctx.meta = (wparams, bparams, act, ldx, ldy, M, N, K)
         return y if ldy == N else y[:, :N]
@@ -83,10 +85,7 @@ class LinearFn(torch.autograd.Function):
         x, weight, saved = ctx.saved_tensors
         wparams, bparams, act, ldx, ldy, M, N, K = ctx.meta
         if act == ACT_GELU:
-            # small matrices only (MLM transform); the FFN uses FfnFn, whose dGELU rides in a GEMM epilogue
-            pre = saved.float()
-            u = pre / 1.41421
-            dy = (dy.float() * (0.5 * (1 + torch.erf(u)) + pre * torch.exp(-u * u) / (1.41421 * math.sqrt(math.pi)))).to(x.dtype)
+            dy = dy * saved                      # saved = gelu'(pre-activation), written by the forward epilogue
         elif act == ACT_TANH:
             yv = saved[:, :N].float()
             dy = (dy.float() * (1 - yv * yv)).to(x.dtype)
