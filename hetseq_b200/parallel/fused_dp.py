@@ -241,14 +241,15 @@ class FusedBackend(AllReduceBackend):
         # very same kernel arguments stay valid when the step is replayed from a CUDA graph
         self.epoch_t = torch.zeros(1, dtype=torch.int32, device=dev)
         # Grids of the kernels that run NEXT TO forward / backward: the fewer CTAs cover the NVLink latency, the
-        # less they take from the GEMMs. Measured (bench.py, BERT-large, graph): 8 GPUs multimem, reduce-scatter
-        # CTAs 148 / 74 / 37 -> 14.38 / 13.56 / 13.46 ms per step, gather 148 -> 37 CTAs another -0.4 ms (13.15);
-        # 4 GPUs multimem, (reduce-scatter, gather) CTAs (74, 37) / (37, 37) / (24, 24) / (16, 16) -> 14.84 / 13.75 /
-        # 14.54 / 15.03 ms: below ~37 the reduction no longer keeps up with backward. Peer loads need (W-1) x more requests in flight: 2 GPUs 148 / 74 / 37 CTAs -> 14.46 / 14.48 / 15.63 ms,
-        # 8 GPUs 296 CTAs 14.56 ms. HETSEQ_RS_BLOCKS / HETSEQ_GATHER_BLOCKS pin other sizes (RS: -1 = one CTA per
-        # owned chunk).
+        # less they take from the GEMMs (which deal their tiles statically: one slowed SM slows the whole GEMM).
+        # Measured (bench.py, BERT-large, graph; (reduce-scatter, gather) CTAs -> ms per step; profiles/scaling.md):
+        #   8 GPUs multimem: (148,148) 14.38  (74,148) 13.56  (37,148) 13.46  (74,37) 13.15  (37,37) 14.41
+        #   4 GPUs multimem: (74,37) 14.84  (37,37) 13.75  (37,16) 13.82  (24,24) 14.54  (16,16) 15.03
+        #   2 GPUs peer loads: (148,148) 14.46  (74,148) 14.48  (37,37) 15.63;  8 GPUs peer loads (296,148) 14.56
+        # i.e. per rank the reduce-scatter wants roughly one CTA per 4-5 MB of owned gradient, and it must not fall
+        # behind backward. HETSEQ_RS_BLOCKS / HETSEQ_GATHER_BLOCKS pin other sizes (RS: -1 = one CTA per owned chunk).
         if self.transport == 'multimem':
-            default_rb, default_gb = 37, 37
+            default_rb, default_gb = (74 if W >= 8 else 37), 37
         else:
             default_rb, default_gb = (148 if W <= 2 else 296), 148
         rb = int(os.environ.get('HETSEQ_RS_BLOCKS', '0') or getattr(args, 'fused_rs_blocks', 0) or default_rb)
