@@ -524,6 +524,11 @@ class NativeBert(object):
         if self.attn_impl is not None and self.attn_impl.supports(B, S, self.heads, H // self.heads, qkv.dtype):
             ctxv = self.attn_impl.attention(qkv, add_mask, B, S, self.heads, p_attn, self.sites[(id(layer), 'attn')])
         else:
+            if not getattr(self, '_warned_composite', False):
+                self._warned_composite = True
+                print('| WARNING: no fused attention kernel for sequence length {} / head size {} (needs a multiple '
+                      'of 16 up to 512 and head size 64): using the PyTorch attention composite'.format(
+                          S, H // self.heads), flush=True)
             ctxv = attention_composite(qkv, add_mask, B, S, self.heads, p_attn, training)
         so = layer.attention.output
         ao = linear(ctxv, so.dense.weight, so.dense.bias, [so.dense.weight], [so.dense.bias])
