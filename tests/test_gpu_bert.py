@@ -153,3 +153,41 @@ def test_cuda_graph_step_matches_eager(tmp_path):
         if a is not None:
             assert abs(a - b) < 2e-2, (le, lg)
     assert (pe - pg).abs().max().item() < 3e-3
+
+
+def test_native_activation_checkpointing_matches(tmp_path):
+    """--checkpoint-activations on the native path: the encoder is recomputed in chunks of ceil(sqrt(L)) layers during
+    backward (reference code path bert_modeling.py:470-476, unreachable there). The recomputation redraws the same
+    Philox dropout masks, so loss and gradients must equal the run without checkpointing (up to the order of the fp32
+    atomics behind the bias / LayerNorm gradients)."""
+    from hetseq_b200.ops import rng
+    ctl, task = _build(str(tmp_path), '--fp16', 'native', num_hidden_layers=5, hidden_dropout_prob=0.1,
+                       attention_probs_dropout_prob=0.1)
+    model = ctl.get_model()
+    dev = task.prepare_sample(_batch(), ctl.device)
+    model.train()
+    out = []
+    for ckpt in (False, True):
+        rng.set_step_seed(777, 0)
+        ctl.zero_grad()
+        loss = model(*dev, checkpoint_activations=ckpt)
+        (loss * 1024.0).backward()
+        ctl.optimizer.buffer.finalize_grads()
+        out.append((loss.item(), ctl.optimizer.buffer.flat_grad.clone()))
+    assert abs(out[0][0] - out[1][0]) < 1e-4, (out[0][0], out[1][0])
+    rel = ((out[0][1] - out[1][1]).norm() / out[0][1].norm()).item()
+    assert rel < 1e-4, rel
+
+
+def test_unsupported_sequence_length_falls_back_with_a_warning(tmp_path, capsys):
+    """S = 72 is not a multiple of 16: the layer keeps the native GEMMs / LayerNorm and takes the PyTorch attention
+    composite, announcing it once (no silent cliff)."""
+    ctl, task = _build(str(tmp_path), '--fp16', 'native')
+    dev = task.prepare_sample(_batch(S=72), ctl.device)
+    model = ctl.get_model()
+    model.train()
+    ctl.zero_grad()
+    loss = model(*dev)
+    (loss * 1024.0).backward()
+    assert loss.item() == loss.item() and 5.0 < loss.item() < 12.0
+    assert 'no fused attention kernel for sequence length 72' in capsys.readouterr().out
