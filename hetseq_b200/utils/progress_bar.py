@@ -14,60 +14,65 @@ from numbers import Number
 from hetseq_b200.utils.meters import AverageMeter, StopwatchMeter, TimeMeter
 
 
-def build_progress_bar(args, iterator, epoch=None, prefix=None, default='simple', no_progress_bar='none'):
-    fmt = getattr(args, 'log_format', None)
-    if fmt is None:
-        fmt = no_progress_bar if getattr(args, 'no_progress_bar', False) else default
-    log_file = getattr(args, 'log_file', None)
-    if fmt == 'json':
-        return json_progress_bar(iterator, epoch, prefix, args.log_interval, log_file)
-    if fmt == 'none':
-        return noop_progress_bar(iterator, epoch, prefix, log_file)
-    if fmt == 'simple':
-        return simple_progress_bar(iterator, epoch, prefix, args.log_interval, log_file)
-    if fmt == 'tqdm':
-        return tqdm_progress_bar(iterator, epoch, prefix, log_file)
-    raise ValueError('Unknown log format: {}'.format(fmt))
+# How each kind of stat is rendered in the text line and what number the machine-readable sinks get. The text
+# forms are the reference's (progress_bar.py:34-44): plain numbers '{:g}', an AverageMeter its average with three
+# decimals, a TimeMeter its rounded rate, a StopwatchMeter its accumulated seconds with four decimals.
+_RENDER = (
+    (AverageMeter, lambda m: '{:.3f}'.format(m.avg), lambda m: m.avg),
+    (TimeMeter, lambda m: '{:g}'.format(round(m.avg)), lambda m: m.avg),
+    (StopwatchMeter, lambda m: '{:.4f}'.format(m.sum), lambda m: m.sum),
+    (Number, lambda x: '{:g}'.format(x), lambda x: x),
+)
 
 
 def format_stat(stat):
-    """Numbers '{:g}', AverageMeter '.3f' of avg, TimeMeter rounded avg, StopwatchMeter '.4f' of sum."""
-    if isinstance(stat, Number):
-        stat = '{:g}'.format(stat)
-    elif isinstance(stat, AverageMeter):
-        stat = '{:.3f}'.format(stat.avg)
-    elif isinstance(stat, TimeMeter):
-        stat = '{:g}'.format(round(stat.avg))
-    elif isinstance(stat, StopwatchMeter):
-        stat = '{:.4f}'.format(stat.sum)
+    """Text form of one stat (anything that is neither a number nor a meter is passed through)."""
+    for kind, text, _ in _RENDER:
+        if isinstance(stat, kind):
+            return text(stat)
     return stat
 
 
 def stat_value(stat):
     """Numeric value of a stat for machine-readable sinks."""
-    if isinstance(stat, AverageMeter):
-        return stat.avg
-    if isinstance(stat, TimeMeter):
-        return stat.avg
-    if isinstance(stat, StopwatchMeter):
-        return stat.sum
-    if isinstance(stat, Number):
-        return stat
+    for kind, _, value in _RENDER:
+        if isinstance(stat, kind):
+            return value(stat)
     return None if stat is None else str(stat)
 
 
+def render(stats, pair='{}={}', sep=', '):
+    """'k=v, k=v' (step lines) or, with pair='{} {}' and sep=' | ', 'k v | k v' (summary lines)."""
+    return sep.join(pair.format(k, str(format_stat(v)).strip()) for k, v in stats.items())
+
+
+def build_progress_bar(args, iterator, epoch=None, prefix=None, default='simple', no_progress_bar='none'):
+    fmt = getattr(args, 'log_format', None) or (no_progress_bar if getattr(args, 'no_progress_bar', False) else default)
+    common = dict(epoch=epoch, prefix=prefix, log_file=getattr(args, 'log_file', None))
+    if fmt in ('json', 'simple'):
+        common['log_interval'] = args.log_interval
+    try:
+        cls = {'json': json_progress_bar, 'none': noop_progress_bar, 'simple': simple_progress_bar,
+               'tqdm': tqdm_progress_bar}[fmt]
+    except KeyError:
+        raise ValueError('Unknown log format: {}'.format(fmt)) from None
+    return cls(iterator, **common)
+
+
 class progress_bar(object):
-    """Base class: iterates the wrapped iterable, subclasses decide what to print."""
+    """Base class: iterates the wrapped iterable, subclasses decide what to print. ``offset`` is where a resumed
+    epoch starts counting."""
 
     def __init__(self, iterable, epoch=None, prefix=None, log_file=None):
         self.iterable = iterable
         self.offset = getattr(iterable, 'offset', 0)
         self.epoch = epoch
-        self.prefix = ''
+        parts = []
         if epoch is not None:
-            self.prefix += '| epoch {:03d}'.format(epoch)
+            parts.append('| epoch {:03d}'.format(epoch))
         if prefix is not None:
-            self.prefix += ' | {}'.format(prefix)
+            parts.append(' | {}'.format(prefix))
+        self.prefix = ''.join(parts)
         self.log_file = log_file
 
     def __len__(self):
@@ -88,17 +93,8 @@ class progress_bar(object):
     def print(self, stats, tag='', step=None):
         raise NotImplementedError
 
-    def _str_commas(self, stats):
-        return ', '.join(key + '=' + stats[key].strip() for key in stats.keys())
-
-    def _str_pipes(self, stats):
-        return ' | '.join(key + ' ' + stats[key].strip() for key in stats.keys())
-
     def _format_stats(self, stats):
-        postfix = OrderedDict(stats)
-        for key in postfix.keys():
-            postfix[key] = str(format_stat(postfix[key]))
-        return postfix
+        return OrderedDict((k, str(format_stat(v))) for k, v in stats.items())
 
     def _json_record(self, stats, i=None, tag=''):
         rec = OrderedDict()
@@ -117,11 +113,19 @@ class progress_bar(object):
             with open(self.log_file, 'a') as f:
                 f.write(json.dumps(rec) + '\n')
 
+    def _steps(self, log_interval):
+        """Yield the items; after item number i (counted from the resume offset) call ``self._emit(i, size)`` when a
+        line is due: stats have been logged, i > 0 and i is a multiple of the interval."""
+        size = len(self.iterable)
+        for i, obj in enumerate(self.iterable, start=self.offset):
+            yield obj
+            if self.stats is not None and i > 0 and log_interval is not None and i % log_interval == 0:
+                self._emit(i, size)
+
 
 class noop_progress_bar(progress_bar):
     def __iter__(self):
-        for obj in self.iterable:
-            yield obj
+        return iter(self.iterable)
 
     def log(self, stats, tag='', step=None):
         if self.log_file:
@@ -138,26 +142,20 @@ class simple_progress_bar(progress_bar):
         super().__init__(iterable, epoch, prefix, log_file)
         self.log_interval = log_interval
         self.stats = None
-        self._raw = None
 
     def __iter__(self):
-        size = len(self.iterable)
-        for i, obj in enumerate(self.iterable, start=self.offset):
-            yield obj
-            if self.stats is not None and i > 0 and self.log_interval is not None \
-                    and i % self.log_interval == 0:
-                postfix = self._str_commas(self.stats)
-                print('{}:  {:5d} / {:d} {}'.format(self.prefix, i, size, postfix), flush=True)
-                if self.log_file:
-                    self._sink(self._json_record(self._raw, i))
+        return self._steps(self.log_interval)
+
+    def _emit(self, i, size):
+        print('{}:  {:5d} / {:d} {}'.format(self.prefix, i, size, render(self.stats)), flush=True)
+        if self.log_file:
+            self._sink(self._json_record(self.stats, i))
 
     def log(self, stats, tag='', step=None):
-        self._raw = stats
-        self.stats = self._format_stats(stats)
+        self.stats = stats
 
     def print(self, stats, tag='', step=None):
-        postfix = self._str_pipes(self._format_stats(stats))
-        print('{} | {}'.format(self.prefix, postfix), flush=True)
+        print('{} | {}'.format(self.prefix, render(stats, '{} {}', ' | ')), flush=True)
 
 
 class json_progress_bar(progress_bar):
@@ -169,16 +167,14 @@ class json_progress_bar(progress_bar):
         self.stats = None
 
     def __iter__(self):
-        size = float(len(self.iterable))
-        for i, obj in enumerate(self.iterable, start=self.offset):
-            yield obj
-            if self.stats is not None and i > 0 and self.log_interval is not None \
-                    and i % self.log_interval == 0:
-                rec = self._json_record(self.stats, i)
-                if self.epoch is not None:
-                    rec['epoch_progress'] = round(self.epoch - 1 + float(i / size), 4)
-                print(json.dumps(rec), flush=True)
-                self._sink(rec)
+        return self._steps(self.log_interval)
+
+    def _emit(self, i, size):
+        rec = self._json_record(self.stats, i)
+        if self.epoch is not None:
+            rec['epoch_progress'] = round(self.epoch - 1 + i / float(size), 4)
+        print(json.dumps(rec), flush=True)
+        self._sink(rec)
 
     def log(self, stats, tag='', step=None):
         self.stats = stats
@@ -211,5 +207,4 @@ class tqdm_progress_bar(progress_bar):
             self._sink(self._json_record(stats, step, tag))
 
     def print(self, stats, tag='', step=None):
-        postfix = self._str_pipes(self._format_stats(stats))
-        self.tqdm.write('{} | {}'.format(self.tqdm.desc, postfix), file=sys.stdout)
+        self.tqdm.write('{} | {}'.format(self.tqdm.desc, render(stats, '{} {}', ' | ')), file=sys.stdout)
