@@ -58,11 +58,14 @@ struct GemmParams {
 // CG = CTAs per MMA (tcgen05 cta_group). CG == 2: a CTA pair owns a 256 x BN tile; each CTA stages its own
 // 128 rows of A and its own BN/2 rows of B (the MMA reads B from both CTAs' smem), so a stage is 32 KiB
 // instead of 48 KiB and the ring is 6 deep -- more bytes in flight per SM for the same shared memory.
-template <int BN, int CG = 1> struct GemmCfg {
-  static constexpr int STAGES = (BN == 256 && CG == 1) ? 4 : 6;
+// TWO_BOX (the epilogue that stores TWO outputs per chunk, GELU and GELU'): a second staging box per epilogue warp
+// so that neither store waits for the other to have been read out of shared memory, paid for with one ring stage.
+template <int BN, int CG = 1, bool TWO_BOX = false> struct GemmCfg {
+  static constexpr int STAGES = TWO_BOX ? 5 : ((BN == 256 && CG == 1) ? 4 : 6);
   static constexpr int B_STAGE_BYTES = (BN / CG) * 128;
   static constexpr int TMEM_COLS = 2 * BN;
-  static constexpr int STAGING_BYTES = EPI_WARPS * 4096;  // one 32-row x 128-byte box per epilogue warp
+  static constexpr int BOX_BYTES = 4096;                  // 32 rows x 128 bytes
+  static constexpr int STAGING_BYTES = EPI_WARPS * BOX_BYTES * (TWO_BOX ? 2 : 1);
   static constexpr int SMEM_BYTES = STAGES * (A_STAGE_BYTES + B_STAGE_BYTES) + STAGING_BYTES +
                                     (2 * STAGES + 4) * 8 /*mbarriers*/ + 16 /*tmem slot*/ + 1024 /*align*/;
 };
@@ -125,10 +128,10 @@ __device__ __forceinline__ void store_row32(T* __restrict__ p, int n0, int N, bo
 // ACT >= 0: the activation is a compile-time constant (the kernel only carries that epilogue: the all-in-one
 // epilogue is ~8.6 K instructions and ncu showed 19 % of the epilogue warps' stalls as instruction fetch);
 // ACT < 0: read it from GemmParams at run time.
-template <int BN, typename InT, typename OutT, int CG, int ACT>
+template <int BN, typename InT, typename OutT, int CG, int ACT, bool TWO_BOX = false>
 __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
                                           const CUtensorMap& tmAux, const GemmParams& p) {
-  using Cfg = GemmCfg<BN, CG>;
+  using Cfg = GemmCfg<BN, CG, TWO_BOX>;
   constexpr int TILE_M = BM * CG;            // rows of C per work item
   const int cta_rank = CG == 2 ? static_cast<int>(cluster_ctarank()) : 0;
   const bool leader = cta_rank == 0;
@@ -283,7 +286,10 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
     constexpr int NCH = (BN / 2) / CW;                  // chunks per tile for this warp
     const int act = ACT >= 0 ? ACT : p.act;
     const bool use_aux = act == HS_ACT_DGELU_MUL || act == HS_ACT_ADD_AUX || act == HS_ACT_MUL_AUX;
-    uint8_t* stg = sStage + (warp - 2) * 4096;
+    // TWO_BOX: the derivative goes through the warp's first box, the output through its second one; each store
+    // then only has to wait for the store of the PREVIOUS chunk from the same box (at most one younger group pending)
+    uint8_t* stg_aux = sStage + (warp - 2) * (Cfg::BOX_BYTES * (TWO_BOX ? 2 : 1));
+    uint8_t* stg = stg_aux + (TWO_BOX ? Cfg::BOX_BYTES : 0);
     // The epilogue operand (pre-activation for dGELU, residual-path gradient for ADD) is this thread's own row:
     // CW 16-bit values = CW/8 16-byte loads. ncu showed the warps stalled on the long scoreboard right after
     // these loads, so they are issued early: an L2 prefetch of the warp's whole part of the tile and the loads
@@ -368,20 +374,23 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
           if (p.aux_out != nullptr) {
             if constexpr (sizeof(OutT) == 2) {
               if (tma) {
-                if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+                if (lane == 0) {
+                  if constexpr (TWO_BOX) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+                  else asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+                }
                 __syncwarp();
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
                   uint4 u;
                   u.x = Cvt<InT>::pack2(av[j * 8 + 0], av[j * 8 + 1]); u.y = Cvt<InT>::pack2(av[j * 8 + 2], av[j * 8 + 3]);
                   u.z = Cvt<InT>::pack2(av[j * 8 + 4], av[j * 8 + 5]); u.w = Cvt<InT>::pack2(av[j * 8 + 6], av[j * 8 + 7]);
-                  *reinterpret_cast<uint4*>(stg + lane * 128 + ((j ^ (lane & 7)) << 4)) = u;
+                  *reinterpret_cast<uint4*>(stg_aux + lane * 128 + ((j ^ (lane & 7)) << 4)) = u;
                 }
                 fence_proxy_async_smem();
                 __syncwarp();
                 if (lane == 0) {
                   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
-                               ::"l"(reinterpret_cast<uint64_t>(&tmAux)), "r"(smem_u32(stg)), "r"(n0), "r"(m0) : "memory");
+                               ::"l"(reinterpret_cast<uint64_t>(&tmAux)), "r"(smem_u32(stg_aux)), "r"(n0), "r"(m0) : "memory");
                   asm volatile("cp.async.bulk.commit_group;" ::: "memory");
                 }
               } else if (row_ok) {
@@ -433,7 +442,10 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
         }
         // ---- output
         if (tma) {
-          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // staging box is free again
+          if (lane == 0) {   // the staging box is free again
+            if constexpr (TWO_BOX) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+            else asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+          }
           __syncwarp();
           if constexpr (sizeof(OutT) == 2) {
 #pragma unroll
@@ -524,12 +536,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
 // CTA-pair variant: tcgen05.mma.cta_group::2 with UMMA_M = 256 (the pair's 256 x 256 tile); one instance per
 // epilogue kind (ACT = -1: generic)
-template <typename InT, typename OutT, int ACT>
+template <typename InT, typename OutT, int ACT, bool TWO_BOX = false>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
 gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                          const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmAux,
                          const GemmParams p) {
-  gemm_body<256, InT, OutT, 2, ACT>(tmA, tmB, tmC, tmAux, p);
+  gemm_body<256, InT, OutT, 2, ACT, TWO_BOX>(tmA, tmB, tmC, tmAux, p);
 }
 
 // ---- host side --------------------------------------------------------------------------------
@@ -624,10 +636,12 @@ int make_tmap_3d_16b(CUtensorMap* out, const void* base, uint64_t inner, uint64_
 
 template <int BN, typename InT, typename OutT, int CG>
 static int launch_gemm(const hs_gemm_args& a, cudaStream_t stream) {
-  using Cfg = GemmCfg<BN, CG>;
   constexpr int TILE_M = BM * CG;
   void (*kern)(CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, GemmParams);
   int variant = 0;
+  int smem_bytes = GemmCfg<BN, CG>::SMEM_BYTES;
+  // HETSEQ_GEMM_TWO_BOX=0: the GELU + GELU' epilogue with one staging box and a 6-deep ring (comparison)
+  static const bool two_box = [] { const char* e = getenv("HETSEQ_GEMM_TWO_BOX"); return e == nullptr || atoi(e) != 0; }();
   if constexpr (CG == 2) {
     kern = gemm_tcgen05_2cta_kernel<InT, OutT, -1>;
     if (a.act == HS_ACT_NONE) { kern = gemm_tcgen05_2cta_kernel<InT, OutT, HS_ACT_NONE>; variant = 1; }
@@ -635,17 +649,22 @@ static int launch_gemm(const hs_gemm_args& a, cudaStream_t stream) {
       if (a.act == HS_ACT_GELU) { kern = gemm_tcgen05_2cta_kernel<InT, OutT, HS_ACT_GELU>; variant = 2; }
       else if (a.act == HS_ACT_DGELU_MUL) { kern = gemm_tcgen05_2cta_kernel<InT, OutT, HS_ACT_DGELU_MUL>; variant = 3; }
       else if (a.act == HS_ACT_ADD_AUX) { kern = gemm_tcgen05_2cta_kernel<InT, OutT, HS_ACT_ADD_AUX>; variant = 4; }
-      else if (a.act == HS_ACT_GELU_DAUX) { kern = gemm_tcgen05_2cta_kernel<InT, OutT, HS_ACT_GELU_DAUX>; variant = 5; }
+      else if (a.act == HS_ACT_GELU_DAUX && !two_box) { kern = gemm_tcgen05_2cta_kernel<InT, OutT, HS_ACT_GELU_DAUX>; variant = 5; }
+      else if (a.act == HS_ACT_GELU_DAUX) {
+        kern = gemm_tcgen05_2cta_kernel<InT, OutT, HS_ACT_GELU_DAUX, true>;
+        variant = 7;
+        smem_bytes = GemmCfg<BN, CG, true>::SMEM_BYTES;
+      }
       else if (a.act == HS_ACT_MUL_AUX) { kern = gemm_tcgen05_2cta_kernel<InT, OutT, HS_ACT_MUL_AUX>; variant = 6; }
     }
   } else {
     kern = gemm_tcgen05_kernel<BN, InT, OutT>;
   }
-  static bool attr_done[64][7] = {};
+  static bool attr_done[64][8] = {};
   int dev = 0;
   HS_CUDA_OK(cudaGetDevice(&dev));
   if (dev < 64 && !attr_done[dev][variant]) {
-    HS_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    HS_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
     attr_done[dev][variant] = true;
   }
   CUtensorMap tmA, tmB;
@@ -713,7 +732,7 @@ static int launch_gemm(const hs_gemm_args& a, cudaStream_t stream) {
     HS_CUDA_OK(cudaMemsetAsync(a.colsum_out, 0, sizeof(float) * a.N, stream));
   const int work = tiles * p.split_k;
   const int grid = (work < sms ? work : sms) * CG;
-  (void)launch_k(kern, dim3(grid), dim3(GEMM_THREADS), Cfg::SMEM_BYTES, stream, tmA, tmB, tmC, tmAux, p);
+  (void)launch_k(kern, dim3(grid), dim3(GEMM_THREADS), smem_bytes, stream, tmA, tmB, tmC, tmAux, p);
   return post_launch("gemm_tcgen05_kernel");
 }
 

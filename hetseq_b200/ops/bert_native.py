@@ -345,9 +345,15 @@ class EmbeddingSumFn(torch.autograd.Function):
         H = de.shape[1]
         bufW = pW._hs_flat[0]
         dW = bufW.ensure_initialized(pW)          # the scatter adds to what the decoder's wgrad left (tied matrix)
+        tg, tacc = _wgrad_target([pT])
+        tg = tg.view(pT.shape)
+        types_done = False
         if len(ctx.saved_tensors) == 4:
-            # segmented reduction over positions sorted by token id: one writer per (token, column), fixed order
-            native.embed_scatter_word_sorted(de, ids, ctx.saved_tensors[2], ctx.saved_tensors[3], dW)
+            # segmented reduction over positions sorted by token id: one writer per (token, column), fixed order;
+            # the two token-type sums come out of the same pass over de
+            types_done = pT.shape[0] == 2 and seg.dtype == ids.dtype and tg.is_contiguous()
+            native.embed_backward_sorted(de, ids, ctx.saved_tensors[2], ctx.saved_tensors[3], dW,
+                                         seg=seg if types_done else None, dT=tg if types_done else None, accumulate_T=tacc)
         else:
             native.embed_scatter_word(de, ids, dW)    # fp32 atomics (HETSEQ_EMBED_ATOMIC=1)
         _notify([pW])
@@ -360,10 +366,9 @@ class EmbeddingSumFn(torch.autograd.Function):
                 pg[S:].zero_()
             native.sum_over_batch(de, B, S * H, pg[:S].reshape(-1), False)
         _notify([pP])
-        tg, tacc = _wgrad_target([pT])
-        tg = tg.view(pT.shape)
-        for t in range(pT.shape[0]):
-            native.colsum_rows_where(de, seg, t, tg[t], tacc)
+        if not types_done:
+            for t in range(pT.shape[0]):
+                native.colsum_rows_where(de, seg, t, tg[t], tacc)
         _notify([pT])
         return None, None, None, None, None, None, None, None, None, None, None
 

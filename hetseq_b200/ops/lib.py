@@ -62,6 +62,8 @@ def load() -> ctypes.CDLL:
     for fn in ('hs_sumsq_scratch_elems',):
         getattr(lib, fn).restype = ctypes.c_int
     lib.hs_colsum_scratch_elems.argtypes = [ctypes.c_int, ctypes.c_int]
+    lib.hs_embed_backward_scratch_elems.argtypes = [ctypes.c_int, ctypes.c_int]
+    lib.hs_embed_backward_scratch_elems.restype = ctypes.c_longlong
     lib.hs_attention_supported.argtypes = [ctypes.c_int, ctypes.c_int]
     lib.hs_dp_signal_words.argtypes = [ctypes.c_int, ctypes.c_int]
     lib.hs_dp_max_gather_buckets.restype = ctypes.c_int

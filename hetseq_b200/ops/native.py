@@ -136,13 +136,23 @@ def embed_scatter_word(de, ids, dW):
                                       dW.shape[0], lib.dtype_code(de.dtype), lib.stream_ptr()), 'hs_embed_scatter_word')
 
 
-def embed_scatter_word_sorted(de, ids, order, run_end, dW):
-    """dW[id] += sum of de rows holding token id, deterministic (segmented reduction over sorted positions)."""
+def embed_backward_sorted(de, ids, order, run_end, dW, seg=None, dT=None, accumulate_T=False):
+    """dW[id] += sum of the rows of de holding token id -- deterministic: segmented reduction over the positions
+    sorted by token id, 16-row segments, one writer and one order of additions per slice of dW. With ``seg`` (token
+    types 0 / 1) and ``dT`` ([2, H] fp32) the same pass also produces the token-type gradient."""
     L = lib.load()
     M, H = de.shape
-    lib.check(L.hs_embed_scatter_word_sorted(de.data_ptr(), ids.data_ptr(), int(ids.dtype == torch.int64),
-                                             order.data_ptr(), run_end.data_ptr(), dW.data_ptr(), M, H, dW.shape[0],
-                                             lib.dtype_code(de.dtype), lib.stream_ptr()), 'hs_embed_scatter_word_sorted')
+    sc = scratch(de.device, int(L.hs_embed_backward_scratch_elems(M, H)), 'embed_bwd')
+    lib.check(L.hs_embed_backward_sorted(de.data_ptr(), ids.data_ptr(), seg.data_ptr() if seg is not None else None,
+                                         int(ids.dtype == torch.int64), order.data_ptr(), run_end.data_ptr(),
+                                         dW.data_ptr(), dT.data_ptr() if dT is not None else None, int(accumulate_T),
+                                         sc.data_ptr(), M, H, dW.shape[0], lib.dtype_code(de.dtype), lib.stream_ptr()),
+              'hs_embed_backward_sorted')
+
+
+def embed_scatter_word_sorted(de, ids, order, run_end, dW):
+    """The word-embedding part of ``embed_backward_sorted`` alone."""
+    embed_backward_sorted(de, ids, order, run_end, dW)
 
 
 def embedding_scatter_plan(ids_flat: torch.Tensor):

@@ -16,7 +16,7 @@ SIGNATURES = {
     'hs_scatter_add_rows': [vp, vp, ci, vp, ci, ci, ci, vp],
     'hs_embed_gather_sum': [vp, vp, vp, vp, vp, ci, vp, ci, ci, ci, ci, ci, ci, vp],
     'hs_embed_scatter_word': [vp, vp, ci, vp, ci, ci, ci, ci, vp],
-    'hs_embed_scatter_word_sorted': [vp, vp, ci, vp, vp, vp, ci, ci, ci, ci, vp],
+    'hs_embed_backward_sorted': [vp, vp, vp, ci, vp, vp, vp, vp, ci, vp, ci, ci, ci, ci, vp],
     'hs_sum_over_batch': [vp, ci, cl, vp, ci, ci, vp],
     'hs_colsum_rows_where': [vp, vp, ci, cl, ci, ci, vp, ci, vp, ci, vp],
     'hs_attention_fwd': [vp, vp, vp, vp, ci, ci, ci, ci, cf, vp, cu, ci, vp],

@@ -173,12 +173,18 @@ HS_API int hs_embed_gather_sum(const void* W, const void* P, const void* Tt, con
 HS_API int hs_embed_scatter_word(const void* de, const void* ids, int ids_i64, float* dW, int M, int H, int vocab,
                                  int dtype, hs_stream_t stream);
 /* Deterministic form of the same scatter-add (the reference's embedding_dense_backward is an atomic scatter,
- * bert_modeling.py:313): order[M] lists the positions sorted by token id (stable), run_end[i] is, for the first
- * sorted slot of each run of equal ids, one past the run's last slot and 0 for every other slot. One thread per
- * (run, 8 columns) sums its rows in slot order and adds the result to dW: bit-identical from run to run. */
-HS_API int hs_embed_scatter_word_sorted(const void* de, const void* ids, int ids_i64, const int* order,
-                                        const int* run_end, float* dW, int M, int H, int vocab, int dtype,
-                                        hs_stream_t stream);
+ * bert_modeling.py:313), and the token-type gradient from the same pass over de. order[M] lists the positions
+ * sorted by token id (stable), run_end[i] is, for the first sorted slot of each run of equal ids, one past the
+ * run's last slot and 0 for every other slot. The sorted slots are cut into 16-row segments (one CTA each, rows
+ * added in slot order); runs that cross segments are completed by a second kernel in segment order, so every
+ * slice of dW has one writer and one order of additions: bit-identical from run to run.
+ * seg / dT: token types (0 or 1) of the positions and the [2, H] fp32 gradient of the token-type table
+ * (overwritten, or added to when accumulate_T); both NULL to leave the token types out.
+ * scratch: hs_embed_backward_scratch_elems(M, H) floats. */
+HS_API long long hs_embed_backward_scratch_elems(int M, int H);
+HS_API int hs_embed_backward_sorted(const void* de, const void* ids, const void* seg, int ids_i64, const int* order,
+                                    const int* run_end, float* dW, float* dT, int accumulate_T, float* scratch,
+                                    int M, int H, int vocab, int dtype, hs_stream_t stream);
 HS_API int hs_sum_over_batch(const void* x, int B, long long inner, float* out, int accumulate, int dtype,
                              hs_stream_t stream);
 HS_API int hs_colsum_rows_where(const void* x, const void* sel, int sel_i64, long long want, int M, int N, float* out,

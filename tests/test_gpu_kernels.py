@@ -330,6 +330,48 @@ def test_embedding_kernels(nat, dt):
     torch.testing.assert_close(dT, refT, rtol=1e-4, atol=1e-3)
 
 
+@pytest.mark.parametrize('dt', DT)
+@pytest.mark.parametrize('M,H,V,wide', [(4096, 1024, 30522, False), (1000, 256, 500, True), (40, 64, 50, False)])
+def test_embedding_backward_sorted_segments(nat, dt, M, H, V, wide):
+    """Word + token-type gradient in one segmented pass (hs_embed_backward_sorted): a quarter of the positions hold
+    one id ([PAD]-like run over dozens of 16-row segments), a tenth another ([MASK]-like), M need not be a multiple
+    of 16, ids outside the table are skipped; against index_add_ in fp32, bit-identical on repeated calls, and the
+    token-type sums with and without accumulation. CPU model of the same logic: tests/test_embed_segments_cpu.py."""
+    from hetseq_b200.tasks.bert import LanguageModelingTask
+    g = torch.Generator(device='cpu').manual_seed(M)
+    ids = torch.randint(3, V, (M,), generator=g)
+    perm = torch.randperm(M, generator=g)
+    ids[perm[: M // 4]] = 0
+    ids[perm[M // 4: M // 4 + M // 10]] = 2
+    if M >= 1000:
+        ids[perm[-3:]] = V + 7                 # not a row of the table
+    idt = torch.int64 if wide else torch.int32
+    seg = torch.randint(0, 2, (M,), generator=g).to(idt).cuda()
+    de = torch.randn(M, H, generator=g).to(dt).cuda()
+    plan = [t.cuda() for t in LanguageModelingTask.embedding_plan(ids)]
+    ids = ids.to(idt).cuda()
+    ok = ids < V
+    refW = torch.ones(V, H, device='cuda').index_add_(0, ids[ok].long(), de[ok].float())
+    refT = torch.zeros(2, H, device='cuda').index_add_(0, seg.long(), de.float())
+    outs = []
+    for _ in range(3):
+        dW = torch.ones(V, H, device='cuda')
+        dT = torch.full((2, H), 5.0, device='cuda')
+        nat.embed_backward_sorted(de, ids, plan[0], plan[1], dW, seg=seg, dT=dT, accumulate_T=False)
+        torch.testing.assert_close(dW, refW, rtol=1e-4, atol=2e-3)
+        torch.testing.assert_close(dT, refT, rtol=1e-4, atol=5e-3)
+        outs.append((dW, dT))
+    for dW, dT in outs[1:]:
+        assert torch.equal(dW, outs[0][0]) and torch.equal(dT, outs[0][1]), 'must be bit-reproducible'
+    dT = torch.full((2, H), 5.0, device='cuda')
+    dW = torch.ones(V, H, device='cuda')
+    nat.embed_backward_sorted(de, ids, plan[0], plan[1], dW, seg=seg, dT=dT, accumulate_T=True)
+    torch.testing.assert_close(dT, refT + 5.0, rtol=1e-4, atol=5e-3)
+    dW2 = torch.ones(V, H, device='cuda')
+    nat.embed_scatter_word_sorted(de, ids, plan[0], plan[1], dW2)          # word part alone
+    assert torch.equal(dW2, outs[0][0])
+
+
 @pytest.mark.parametrize('kind', ['adam', 'adadelta'])
 @pytest.mark.parametrize('dt', [torch.float16, torch.float32])
 def test_fused_optimizer_matches_per_tensor(kind, dt):
