@@ -343,13 +343,47 @@ __device__ __forceinline__ float gelu_grad_ref(float x) {
   return 0.5f * (1.0f + erf_poly(u)) + x * __expf(-u * u) * (0.5641895835477563f * kGeluInv);
 }
 
-// gelu(x) and gelu'(x) together (they share the erf): forward can store the derivative for backward
+// gelu(x) and gelu'(x) together (they share the erf): forward can store the derivative for backward.
+// This is the epilogue of the largest GEMM of a layer (64 elements per thread per chunk), so the arithmetic is
+// folded as far as it goes -- 22 instructions per element instead of 30: the polynomial takes x itself
+// (coefficients of 0.5 * erf(x / 1.41421) = x * Q(x^2), so the scaling of the argument, the "1 +" and the "0.5 *"
+// disappear into Q and one final add), and exp(-(x / 1.41421)^2) is one multiply + ex2.approx.ftz (no
+// denormal-range fix-up: below 2^-126 the term is 0 in the 16-bit output anyway).
+namespace gelu_q {
+constexpr double S = 1.0 / 1.41421, S2 = S * S;
+constexpr double H1 = 0.5 * S, H3 = H1 * S2, H5 = H3 * S2, H7 = H5 * S2, H9 = H7 * S2, H11 = H9 * S2, H13 = H11 * S2,
+                 H15 = H13 * S2, H17 = H15 * S2;
+constexpr float Q0 = static_cast<float>(H1 * 1.1282684529e+00), Q1 = static_cast<float>(H3 * -3.7531502903e-01),
+                Q2 = static_cast<float>(H5 * 1.1107960747e-01), Q3 = static_cast<float>(H7 * -2.5103073778e-02),
+                Q4 = static_cast<float>(H9 * 4.2355141407e-03), Q5 = static_cast<float>(H11 * -5.1105671781e-04),
+                Q6 = static_cast<float>(H13 * 4.1063089266e-05), Q7 = static_cast<float>(H15 * -1.9449973089e-06),
+                Q8 = static_cast<float>(H17 * 4.0746968943e-08);
+constexpr float XMAX = static_cast<float>(3.0 / S);                       // |x / 1.41421| <= 3
+constexpr float EXP2_SCALE = static_cast<float>(-S2 * 1.4426950408889634);   // exp(-(x S)^2) = 2^(x^2 * EXP2_SCALE)
+constexpr float PDF_SCALE = static_cast<float>(0.5641895835477563 * S);    // d/dx of 0.5 erf(x S) = PDF_SCALE * exp(..)
+}  // namespace gelu_q
+__device__ __forceinline__ float ex2_ftz(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 __device__ __forceinline__ void gelu_and_grad(const float x_in, float& y, float& dy) {
+  using namespace gelu_q;
   const float x = x_in;     // y may alias the argument
-  const float u = x * kGeluInv;
-  const float cdf = 0.5f * (1.0f + erf_poly(u));
+  const float xc = fminf(fmaxf(x, -XMAX), XMAX);
+  const float t = xc * xc;
+  float q = Q8;
+  q = fmaf(q, t, Q7);
+  q = fmaf(q, t, Q6);
+  q = fmaf(q, t, Q5);
+  q = fmaf(q, t, Q4);
+  q = fmaf(q, t, Q3);
+  q = fmaf(q, t, Q2);
+  q = fmaf(q, t, Q1);
+  q = fmaf(q, t, Q0);
+  const float cdf = fminf(fmaxf(q * xc, -0.5f), 0.5f) + 0.5f;
   y = x * cdf;
-  dy = cdf + x * __expf(-u * u) * (0.5641895835477563f * kGeluInv);
+  dy = fmaf(x * ex2_ftz(x * x * EXP2_SCALE), PDF_SCALE, cdf);
 }
 
 // ----------------------------------------------------------------------------------------------
