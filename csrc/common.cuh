@@ -345,7 +345,7 @@ __device__ __forceinline__ float gelu_grad_ref(float x) {
 
 // gelu(x) and gelu'(x) together (they share the erf): forward can store the derivative for backward.
 // This is the epilogue of the largest GEMM of a layer (64 elements per thread per chunk), so the arithmetic is
-// folded as far as it goes -- 22 instructions per element instead of 30: the polynomial takes x itself
+// folded as far as it goes -- 19 instructions per element instead of 30: the polynomial takes x itself
 // (coefficients of 0.5 * erf(x / 1.41421) = x * Q(x^2), so the scaling of the argument, the "1 +" and the "0.5 *"
 // disappear into Q and one final add), and exp(-(x / 1.41421)^2) is one multiply + ex2.approx.ftz (no
 // denormal-range fix-up: below 2^-126 the term is 0 in the 16-bit output anyway).
@@ -381,7 +381,7 @@ __device__ __forceinline__ void gelu_and_grad(const float x_in, float& y, float&
   q = fmaf(q, t, Q2);
   q = fmaf(q, t, Q1);
   q = fmaf(q, t, Q0);
-  const float cdf = fminf(fmaxf(q * xc, -0.5f), 0.5f) + 0.5f;
+  const float cdf = fmaf(q, xc, 0.5f);    // |q * xc| <= 0.4999987 on the clamped domain (checked over a 1e-5 grid): no second clamp
   y = x * cdf;
   dy = fmaf(x * ex2_ftz(x * x * EXP2_SCALE), PDF_SCALE, cdf);
 }

@@ -336,29 +336,36 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
         const int n0 = n_base + c0;
         if (n0 >= p.N) break;  // warp-uniform
         float v[CW];
+        const bool bias_vec = add_bias && n0 + CW <= p.N;
 #pragma unroll
         for (int sub = 0; sub < CW / 32; ++sub) {
           uint32_t r[32];
           tmem_ld_32x32(t_row + c0 + sub * 32, r);
-          tmem_ld_wait();
+          if (bias_vec) {
+            // bias loads go out under the TMEM read; alpha and the bias are one FMA per element
+            uint4 bu[4];
 #pragma unroll
-          for (int i = 0; i < 32; ++i) v[sub * 32 + i] = __uint_as_float(r[i]) * alpha;
-        }
-        if (add_bias) {
-          if (n0 + CW <= p.N) {
+            for (int j = 0; j < 4; ++j) bu[j] = *reinterpret_cast<const uint4*>(bias + n0 + sub * 32 + j * 8);
+            tmem_ld_wait();
 #pragma unroll
-            for (int j = 0; j < CW / 8; ++j) {
-              const uint4 u = *reinterpret_cast<const uint4*>(bias + n0 + j * 8);
-              const float2 f0 = Cvt<InT>::unpack2(u.x), f1 = Cvt<InT>::unpack2(u.y), f2 = Cvt<InT>::unpack2(u.z),
-                           f3 = Cvt<InT>::unpack2(u.w);
-              v[j * 8 + 0] += f0.x; v[j * 8 + 1] += f0.y; v[j * 8 + 2] += f1.x; v[j * 8 + 3] += f1.y;
-              v[j * 8 + 4] += f2.x; v[j * 8 + 5] += f2.y; v[j * 8 + 6] += f3.x; v[j * 8 + 7] += f3.y;
+            for (int j = 0; j < 4; ++j) {
+              const float2 f0 = Cvt<InT>::unpack2(bu[j].x), f1 = Cvt<InT>::unpack2(bu[j].y), f2 = Cvt<InT>::unpack2(bu[j].z),
+                           f3 = Cvt<InT>::unpack2(bu[j].w);
+              const float bf[8] = {f0.x, f0.y, f1.x, f1.y, f2.x, f2.y, f3.x, f3.y};
+#pragma unroll
+              for (int i = 0; i < 8; ++i)
+                v[sub * 32 + j * 8 + i] = fmaf(__uint_as_float(r[j * 8 + i]), alpha, bf[i]);
             }
           } else {
+            tmem_ld_wait();
 #pragma unroll
-            for (int i = 0; i < CW; ++i)
-              if (n0 + i < p.N) v[i] += Cvt<InT>::to_f(bias[n0 + i]);
+            for (int i = 0; i < 32; ++i) v[sub * 32 + i] = __uint_as_float(r[i]) * alpha;
           }
+        }
+        if (add_bias && !bias_vec) {
+#pragma unroll
+          for (int i = 0; i < CW; ++i)
+            if (n0 + i < p.N) v[i] += Cvt<InT>::to_f(bias[n0 + i]);
         }
         // ---- activation (pre-activation goes out first when requested)
         if (act == HS_ACT_GELU || act == HS_ACT_GELU_DAUX) {
