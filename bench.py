@@ -257,6 +257,14 @@ def run_ours(a):
             total = sum(int(k.count) for k in prof.key_averages()
                         if k.device_time_total > 0 and 'Memcpy' not in k.key and 'Memset' not in k.key)
             other_launches = max(0, total - int(launches_per_step))
+            dump = os.environ.get('HETSEQ_BENCH_KERNEL_LIST')      # diagnosis: every kernel of that update, by name
+            if dump and int(os.environ.get('RANK', '0')) == 0:
+                rows = sorted(((k.key, int(k.count), float(k.device_time_total)) for k in prof.key_averages()
+                               if k.device_time_total > 0), key=lambda r: -r[2])
+                with open(dump, 'w') as f:
+                    f.write('count\tdevice_us\tkernel (one eager update, CUPTI)\n')
+                    for name, cnt, us in rows:
+                        f.write('%d\t%.1f\t%s\n' % (cnt, us, name[:160]))
         except Exception:        # noqa: BLE001
             other_launches = None
 
