@@ -214,6 +214,11 @@ class _Optimizer(object):
         return compact.view(-1, CHUNK) if self.sharded else compact
 
     def _local_sumsq(self) -> torch.Tensor:
+        take = getattr(self.dp, 'take_local_sumsq', None)     # measured bucket by bucket during backward
+        if take is not None:
+            done = take()
+            if done is not None:
+                return done
         g = self._owned(self.buffer.flat_grad)
         if self._native is not None:
             return self._native.sumsq(g)

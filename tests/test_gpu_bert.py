@@ -155,6 +155,47 @@ def test_cuda_graph_step_matches_eager(tmp_path):
     assert (pe - pg).abs().max().item() < 3e-3
 
 
+def test_gradient_norm_taken_during_backward_matches_single_pass(tmp_path, monkeypatch):
+    """One GPU: the norm's sum of squares comes from per-bucket kernels on a side stream, started by the
+    gradient-ready callbacks while backward runs (parallel/data_parallel.py::LocalNormBackend). Against the single
+    pass over the flat gradient after backward (HETSEQ_NORM_OVERLAP=0): same gnorm up to the order of the fp32
+    additions, same parameters after a few updates, in eager and in CUDA-graph steps; the graph must contain the
+    side stream's work (a fork that is not joined would fail the capture)."""
+    from hetseq_b200.data.bert_dataset import SyntheticBertData
+    from hetseq_b200.parallel import data_parallel
+    ds = SyntheticBertData(64, 128, 10, 2000, seed=7)
+    batches = [ds.fetch_rows(list(range(i * 8, i * 8 + 8))) for i in range(6)]
+    res = {}
+    for mode in ('single', 'overlap', 'overlap-graph'):
+        monkeypatch.setenv('HETSEQ_NORM_OVERLAP', '0' if mode == 'single' else '1')
+        monkeypatch.setattr(data_parallel.LocalNormBackend, 'NORM_BUCKET_MB', 1)    # several buckets on this small model
+        d = os.path.join(str(tmp_path), mode)
+        os.makedirs(d)
+        ctl, task = _build(d, '--fp16', 'native', seed=0)
+        graph = mode.endswith('graph')
+        ctl.args.cuda_graph = graph
+        ctl._graph_enabled = graph
+        assert isinstance(ctl.dp, data_parallel.LocalNormBackend) == (mode != 'single')
+        if mode != 'single':
+            assert len(ctl.dp.buckets) > 3
+        norms = []
+        for b in batches:
+            out = ctl.train_step([b])
+            norms.append(None if out is None else float(ctl._prev_grad_norm))
+        if graph:
+            assert ctl._graph is not None, 'the step was never captured'
+        res[mode] = (norms, ctl.buffer.flat_param.detach().float().clone(), ctl.get_num_updates())
+    n0, p0, u0 = res['single']
+    for mode in ('overlap', 'overlap-graph'):
+        n1, p1, u1 = res[mode]
+        assert u0 == u1
+        for a, b in zip(n0, n1):
+            assert (a is None) == (b is None)
+            if a is not None:
+                assert abs(a - b) <= 2e-3 * max(1.0, abs(a)), (mode, n0, n1)
+        assert (p0 - p1).abs().max().item() < 3e-3
+
+
 def test_native_activation_checkpointing_matches(tmp_path):
     """--checkpoint-activations on the native path: the encoder is recomputed in chunks of ceil(sqrt(L)) layers during
     backward (reference code path bert_modeling.py:470-476, unreachable there). The recomputation redraws the same
