@@ -81,23 +81,29 @@ class Controller(object):
         self.init_meters(args)
 
     # -- meters -----------------------------------------------------------------------------------
+    #: name -> (meter class, what it measures); order = order of the columns in the training log line. 'oom' is
+    #: looked up by the reference's train loop but never created there; 'loss_scale' only exists under --fp16.
+    METER_SCHEMA = (
+        ('train_loss', AverageMeter, 'training loss per sample, base 2'),
+        ('train_nll_loss', AverageMeter, 'same, negative log-likelihood part'),
+        ('valid_loss', AverageMeter, 'validation loss'),
+        ('valid_nll_loss', AverageMeter, 'validation nll'),
+        ('wps', TimeMeter, 'words per second'),
+        ('ups', TimeMeter, 'updates per second'),
+        ('wpb', AverageMeter, 'words per batch'),
+        ('bsz', AverageMeter, 'sentences per batch'),
+        ('gnorm', AverageMeter, 'gradient norm'),
+        ('clip', AverageMeter, 'share of updates that were clipped'),
+        ('oom', AverageMeter, 'out-of-memory batches'),
+        ('loss_scale', AverageMeter, 'dynamic loss scale'),
+        ('wall', TimeMeter, 'wall time in seconds'),
+        ('train_wall', StopwatchMeter, 'time spent inside train_step'),
+    )
+
     def init_meters(self, args):
-        self.meters = OrderedDict()
-        self.meters['train_loss'] = AverageMeter()
-        self.meters['train_nll_loss'] = AverageMeter()
-        self.meters['valid_loss'] = AverageMeter()
-        self.meters['valid_nll_loss'] = AverageMeter()
-        self.meters['wps'] = TimeMeter()       # words per second
-        self.meters['ups'] = TimeMeter()       # updates per second
-        self.meters['wpb'] = AverageMeter()    # words per batch
-        self.meters['bsz'] = AverageMeter()    # sentences per batch
-        self.meters['gnorm'] = AverageMeter()  # gradient norm
-        self.meters['clip'] = AverageMeter()   # % of updates clipped
-        self.meters['oom'] = AverageMeter()    # out of memory (the reference looks this meter up but never creates it)
-        if getattr(args, 'fp16', False):
-            self.meters['loss_scale'] = AverageMeter()  # dynamic loss scale
-        self.meters['wall'] = TimeMeter()      # wall time in seconds
-        self.meters['train_wall'] = StopwatchMeter()  # train wall time in seconds
+        fp16 = bool(getattr(args, 'fp16', False))
+        self.meters = OrderedDict((name, cls()) for name, cls, _ in self.METER_SCHEMA
+                                  if name != 'loss_scale' or fp16)
 
     # -- lazily built engine ------------------------------------------------------------------------
     @property
