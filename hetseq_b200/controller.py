@@ -202,51 +202,56 @@ class Controller(object):
 
     def load_checkpoint(self, filename, reset_optimizer=False, reset_lr_scheduler=False,
                         optimizer_overrides=None, reset_meters=False):
-        """Load all training state from a checkpoint file (every rank reads the file itself)."""
-        extra_state, self._optim_history, last_optim_state = None, [], None
+        """Restore training state from ``filename`` (every rank reads the file itself) in three steps -- weights,
+        optimizer + schedule, progress -- and return the saved ``extra_state`` (None when there is nothing to
+        resume from). Same messages and semantics as the reference (controller.py:138-200)."""
         if self._dp is not None:
             self._dp.flush()
+        self._optim_history = []
+        if not os.path.exists(filename):
+            print('| no existing checkpoint found {}'.format(filename))
+            return None
+        state = checkpoint_utils.load_checkpoint_to_cpu(filename)
+        self._restore_weights(state, filename)
+        self._optim_history = state['optimizer_history']
+        if state.get('last_optimizer_state') is not None and not reset_optimizer:
+            self._restore_optimizer(state['last_optimizer_state'], reset_lr_scheduler, optimizer_overrides)
+        return self._restore_progress(state['extra_state'], filename, reset_meters)
 
-        if os.path.exists(filename):
-            state = checkpoint_utils.load_checkpoint_to_cpu(filename)
-            try:
-                self.get_model().load_state_dict(state['model'], strict=True)
-            except Exception:
-                raise Exception('Cannot load model parameters from checkpoint {}; please ensure that the '
-                                'architectures match.'.format(filename))
-            extra_state = state['extra_state']
-            self._optim_history = state['optimizer_history']
-            last_optim_state = state.get('last_optimizer_state', None)
-            if self._optimizer is not None:
-                self._optimizer.refresh_master()
+    def _restore_weights(self, state, filename):
+        try:
+            self.get_model().load_state_dict(state['model'], strict=True)
+        except Exception:
+            raise Exception('Cannot load model parameters from checkpoint {}; please ensure that the '
+                            'architectures match.'.format(filename))
+        if self._optimizer is not None:
+            self._optimizer.refresh_master()
 
-        if last_optim_state is not None and not reset_optimizer:
-            self._build_optimizer()   # rebuild after loading the model, params may have changed
-            last_optim = self._optim_history[-1]
-            assert last_optim['optimizer_name'] == self.optimizer.__class__.__name__, \
-                'Optimizer does not match; please reset the optimizer (--reset-optimizer).'
-            if not reset_lr_scheduler:
-                self.lr_scheduler.load_state_dict(last_optim['lr_scheduler_state'])
-            self.optimizer.load_state_dict(self._canonical_to_buffer_order(last_optim_state), optimizer_overrides)
-            self.set_num_updates(last_optim['num_updates'])
+    def _restore_optimizer(self, optim_state, reset_lr_scheduler, overrides):
+        self._build_optimizer()   # after the weights: the fp32 master copy is taken from them
+        last = self._optim_history[-1]
+        assert last['optimizer_name'] == self.optimizer.__class__.__name__, \
+            'Optimizer does not match; please reset the optimizer (--reset-optimizer).'
+        if not reset_lr_scheduler:
+            self.lr_scheduler.load_state_dict(last['lr_scheduler_state'])
+        self.optimizer.load_state_dict(self._canonical_to_buffer_order(optim_state), overrides)
+        self.set_num_updates(last['num_updates'])
 
-        if extra_state is not None and 'train_iterator' in extra_state:
-            epoch = extra_state['train_iterator']['epoch']
-            print('| loaded checkpoint {} (epoch {} @ {} updates)'.format(filename, epoch, self.get_num_updates()))
-            self.lr_step(epoch)
-            if 'train_meters' in extra_state and not reset_meters:
-                self.meters.update(extra_state['train_meters'])
-                del extra_state['train_meters']
-                for meter in self.meters.values():
-                    if isinstance(meter, TimeMeter):
-                        meter.reset()
-        elif os.path.exists(filename):
+    def _restore_progress(self, extra_state, filename, reset_meters):
+        if not extra_state or 'train_iterator' not in extra_state:
             # a file written by the reference itself: extra_state == {} (checkpoint_utils.py:204)
             print('| loaded checkpoint {} without iterator state (@ {} updates)'.format(
                 filename, self.get_num_updates()))
-            extra_state = None
-        else:
-            print('| no existing checkpoint found {}'.format(filename))
+            return None
+        epoch = extra_state['train_iterator']['epoch']
+        print('| loaded checkpoint {} (epoch {} @ {} updates)'.format(filename, epoch, self.get_num_updates()))
+        self.lr_step(epoch)
+        saved = extra_state.pop('train_meters', None)
+        if saved is not None and not reset_meters:
+            self.meters.update(saved)
+            for meter in self.meters.values():
+                if isinstance(meter, TimeMeter):
+                    meter.reset()
         return extra_state
 
     def _buffer_to_canonical_order(self, opt_state):
