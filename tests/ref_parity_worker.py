@@ -177,6 +177,78 @@ def check_bert_loss_and_grads():
     assert abs(lr.item() - lm2.item()) < 1e-5
 
 
+def check_all_heads():
+    """Every model class the reference exports (BertModel and the six task heads, bert_modeling.py:736-1290): same
+    state-dict keys, and with the reference's weights loaded the same outputs -- logits without labels, loss with
+    labels, and the gradient of that loss for every parameter."""
+    import torch
+    import bert_modeling as ref_bm
+    from hetseq_b200.models import bert as my_bm
+    cfg = dict(vocab_size=90, hidden_size=32, num_hidden_layers=2, num_attention_heads=4, intermediate_size=64,
+               hidden_act='gelu', hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0,
+               max_position_embeddings=24, type_vocab_size=2, initializer_range=0.02)
+    B, S, C = 3, 12, 4
+    g = torch.Generator().manual_seed(3)
+    ids = torch.randint(0, 90, (B, S), generator=g)
+    seg = torch.randint(0, 2, (B, S), generator=g)
+    mask = torch.ones(B, S, dtype=torch.long)
+    mask[2, 8:] = 0
+    mlm = torch.full((B, S), -1, dtype=torch.long)
+    mlm[0, 2], mlm[1, 7], mlm[2, 3] = 5, 9, 11
+    cases = [
+        ('BertForMaskedLM', (), dict(masked_lm_labels=mlm)),
+        ('BertForNextSentencePrediction', (), dict(next_sentence_label=torch.tensor([1, 0, 1]))),
+        ('BertForSequenceClassification', (5,), dict(labels=torch.tensor([4, 0, 2]))),
+        ('BertForTokenClassification', (6,), dict(labels=torch.randint(0, 6, (B, S), generator=g))),
+        ('BertForQuestionAnswering', (), dict(start_positions=torch.tensor([1, 5, 40]), end_positions=torch.tensor([3, 9, 2]))),
+    ]
+    for name, extra, labels in cases:
+        torch.manual_seed(1)
+        ref = getattr(ref_bm, name)(ref_bm.BertConfig.from_dict(cfg), *extra).float()
+        mine = getattr(my_bm, name)(my_bm.BertConfig.from_dict(cfg), *extra).float()
+        assert list(ref.state_dict().keys()) == list(mine.state_dict().keys()), name + ': state-dict keys differ'
+        mine.load_state_dict(ref.state_dict())
+        ref.eval()
+        mine.eval()
+        with torch.no_grad():
+            a, b = ref(ids, seg, mask), mine(ids, seg, mask)
+        a, b = (a, b) if isinstance(a, tuple) else ((a,), (b,))
+        for x, y in zip(a, b):
+            assert x.shape == y.shape and torch.allclose(x, y, rtol=1e-4, atol=1e-5), name + ': logits differ'
+        la, lb = ref(ids, seg, mask, **labels), mine(ids, seg, mask, **labels)
+        assert abs(la.item() - lb.item()) < 1e-5, (name, la.item(), lb.item())
+        la.backward()
+        lb.backward()
+        gr = dict(ref.named_parameters())
+        for pn, p in mine.named_parameters():
+            ga, gb = gr[pn].grad, p.grad
+            assert (ga is None) == (gb is None), (name, pn)
+            if ga is not None:
+                assert torch.allclose(ga, gb, rtol=1e-4, atol=1e-6), (name, pn, (ga - gb).abs().max().item())
+    # multiple choice: inputs are [B, choices, S]
+    torch.manual_seed(1)
+    ref = ref_bm.BertForMultipleChoice(ref_bm.BertConfig.from_dict(cfg), C).float().eval()
+    mine = my_bm.BertForMultipleChoice(my_bm.BertConfig.from_dict(cfg), C).float().eval()
+    mine.load_state_dict(ref.state_dict())
+    ids4 = torch.randint(0, 90, (B, C, S), generator=g)
+    seg4 = torch.randint(0, 2, (B, C, S), generator=g)
+    mask4 = torch.ones(B, C, S, dtype=torch.long)
+    lab = torch.tensor([3, 0, 1])
+    with torch.no_grad():
+        assert torch.allclose(ref(ids4, seg4, mask4), mine(ids4, seg4, mask4), rtol=1e-4, atol=1e-5)
+        assert abs(ref(ids4, seg4, mask4, lab).item() - mine(ids4, seg4, mask4, lab).item()) < 1e-5
+    # the trunk: all encoder layers and the pooled output
+    torch.manual_seed(1)
+    ref = ref_bm.BertModel(ref_bm.BertConfig.from_dict(cfg)).float().eval()
+    mine = my_bm.BertModel(my_bm.BertConfig.from_dict(cfg)).float().eval()
+    mine.load_state_dict(ref.state_dict())
+    with torch.no_grad():
+        (la, pa), (lb, pb) = ref(ids, seg, mask), mine(ids, seg, mask)
+    assert len(la) == len(lb) == 2 and torch.allclose(pa, pb, rtol=1e-4, atol=1e-5)
+    for x, y in zip(la, lb):
+        assert torch.allclose(x, y, rtol=1e-4, atol=1e-5)
+
+
 def check_meters_and_format():
     import meters as ref_m
     import progress_bar as ref_pb
@@ -407,7 +479,7 @@ def check_bert_training_curve():
 
 
 CHECKS = [check_bert_training_curve, check_mnist_training_curve, check_checkpoint_interchange, check_lr_schedule, check_optimizers, check_iterators, check_batch_by_size, check_bert_loss_and_grads,
-          check_meters_and_format, check_flag_defaults]
+          check_all_heads, check_meters_and_format, check_flag_defaults]
 
 
 def main():

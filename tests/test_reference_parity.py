@@ -1,6 +1,6 @@
 """This framework against the UNMODIFIED reference (baseline/_ref) used as an oracle, component by component, on
 CPU: LR schedule, Adam / Adadelta math, iterators, the batch planner vs the reference's Cython extension, the BERT
-pre-training loss and every parameter gradient, checkpoint files in both directions, meters / log formatting, flag names and defaults.
+pre-training loss and every parameter gradient, BertModel and the six task heads (logits, loss, gradients), checkpoint files in both directions, meters / log formatting, flag names and defaults.
 
 The checks run in a separate interpreter (tests/ref_parity_worker.py) because the reference uses flat module names
 (``utils``, ``data``, ``options`` ...). Skipped when the reference is not installed (baseline/install_reference.sh)."""
@@ -13,7 +13,7 @@ import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CHECKS = ['check_bert_training_curve', 'check_mnist_training_curve', 'check_checkpoint_interchange', 'check_lr_schedule', 'check_optimizers', 'check_iterators', 'check_batch_by_size',
-          'check_bert_loss_and_grads', 'check_meters_and_format', 'check_flag_defaults']
+          'check_bert_loss_and_grads', 'check_all_heads', 'check_meters_and_format', 'check_flag_defaults']
 _cache = {}
 
 
