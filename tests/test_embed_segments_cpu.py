@@ -130,3 +130,30 @@ def test_device_plan_and_host_plan_agree():
     a = native.embedding_scatter_plan(ids)
     b = LanguageModelingTask.embedding_plan(ids)
     assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
+
+
+def test_segment_model_fuzz():
+    """Property test over random batches: any length, tiny vocabularies (so runs of every length and alignment
+    relative to the 16-slot segments occur), ids outside the table mixed in."""
+    hypothesis = pytest.importorskip('hypothesis')
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=120, deadline=None)
+    @given(st.integers(1, 200), st.integers(1, 12), st.integers(0, 2 ** 31 - 1), st.booleans())
+    def prop(M, vocab, seed, with_bad):
+        g = np.random.default_rng(seed)
+        lo, hi = (-2, vocab + 2) if with_bad else (0, vocab)
+        ids = g.integers(lo, hi, size=M).astype(np.int64)
+        seg = g.integers(0, 2, size=M).astype(np.int64)
+        de = g.integers(-8, 9, size=(M, 8)).astype(np.float16)     # small integers: every order of additions is exact
+        order, run_end = (t.numpy() for t in LanguageModelingTask.embedding_plan(torch.from_numpy(ids)))
+        dW = np.zeros((vocab, 8), dtype=np.float32)
+        dT = model_backward(de, ids, seg, order, run_end, dW, vocab)
+        ok = (ids >= 0) & (ids < vocab)
+        refW = np.zeros((vocab, 8), dtype=np.float32)
+        np.add.at(refW, ids[ok], de[ok].astype(np.float32))
+        refT = np.zeros((2, 8), dtype=np.float32)
+        np.add.at(refT, seg, de.astype(np.float32))
+        assert np.array_equal(dW, refW) and np.array_equal(dT, refT)
+
+    prop()
