@@ -50,3 +50,17 @@ def test_scratch_size_helpers():
     assert int(L.hs_embed_backward_scratch_elems(4096, 1024)) == (4096 // 16) * 4 * 1024
     assert int(L.hs_embed_backward_scratch_elems(17, 64)) == 2 * 4 * 64
     assert int(L.hs_version()) >= 100
+
+
+def test_launch_without_a_gpu_is_a_loud_error():
+    """No silent fallback: on a machine without a usable GPU a kernel entry point returns an error that the binding
+    turns into an exception naming the kernel and the CUDA reason."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip('needs a machine without a GPU')
+    L = lib.load()
+    x, out, sc = torch.zeros(4096), torch.zeros(1), torch.zeros(int(L.hs_sumsq_scratch_elems()) + 8)
+    rc = L.hs_sumsq(x.data_ptr(), lib.dtype_code(torch.float32), 2, 2048, 2048, sc.data_ptr(), out.data_ptr(), 0, None)
+    assert rc != 0
+    with pytest.raises(RuntimeError, match='hs_sumsq failed'):
+        lib.check(rc, 'hs_sumsq')
