@@ -205,3 +205,33 @@ def test_sharded_iterator_padding_and_generators():
         ShardedIterator(Sized(3), 2, 2)
     g = GroupedIterator(Sized(7), 3)
     assert len(g) == 3 and list(g) == [[0, 10, 20], [30, 40, 50], [60]]
+
+
+def test_training_budget_and_per_epoch_lists():
+    """Stop rules of the epoch driver (reference train.py:74-88) and the per-epoch flag lists (--update-freq 4 2 1
+    means 4 in epoch 1, 2 in epoch 2, 1 from epoch 3 on; reference train.py:113-116)."""
+    import argparse
+    from hetseq_b200.train import _Budget, _per_epoch
+
+    assert [_per_epoch([4, 2, 1], e) for e in (1, 2, 3, 7)] == [4, 2, 1, 1]
+    assert _per_epoch([3], 5) == 3
+
+    class Ctl(object):
+        def __init__(self, n):
+            self.n = n
+
+        def get_num_updates(self):
+            return self.n
+
+    class Itr(object):
+        def __init__(self, epoch, pending=None):
+            self.epoch, self._next_epoch_itr = epoch, pending
+
+    b = _Budget(argparse.Namespace(min_lr=1e-5, max_epoch=3, max_update=100))
+    assert b.keep_going(Ctl(10), Itr(2), 1e-3)
+    assert not b.keep_going(Ctl(100), Itr(2), 1e-3)            # --max-update reached
+    assert not b.keep_going(Ctl(10), Itr(3), 1e-3)             # --max-epoch epochs done
+    assert b.keep_going(Ctl(10), Itr(3, pending=object()), 1e-3)   # resumed in the middle of the last epoch
+    assert not b.keep_going(Ctl(10), Itr(1), 1e-5)             # learning rate fell to --min-lr
+    unlimited = _Budget(argparse.Namespace(min_lr=-1.0, max_epoch=0, max_update=0))
+    assert unlimited.keep_going(Ctl(10 ** 9), Itr(10 ** 6), 0.0)
